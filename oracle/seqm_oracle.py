@@ -376,7 +376,7 @@ def overlap(ni, nj, xij, rij, zeta_a, zeta_b):
     S221 = torch.where(xx, -pre * (B[2] * (A[4] + A[0]) - A[2] * (B[4] + B[0])), zero)
     S222 = torch.where(xx, 0.5 * pre * (A[4] * (B[0] - B[2]) - B[4] * (A[0] - A[2]) - A[2] * B[0] + B[2] * A[0]), zero)
     # direction cosines (:24-45)
-    xy = torch.sqrt(xij[:, 0] ** 2 + xij[:, 1] ** 2)
+    xy = torch.norm(xij[:, :2], dim=1)        # zero sub-gradient on the z axis, as the reference's norm
     gen = xy >= 1.0e-10
     sgn = torch.sign(xij[:, 2]).detach()
     xys = torch.where(gen, xy, torch.ones_like(xy))
