@@ -1,0 +1,170 @@
+/*
+ * seqm_b200 — C ABI of the B200 (sm_100a) kernels behind PYSEQM's batched SCF hot path.
+ *
+ * The reference (mtzgroup/PYSEQM) is pure Python/PyTorch and has no FFI of its own; the boundary it
+ * offers is the Python call surface of seqm/basics.py and seqm/seqm_functions/*.py.  Each entry point
+ * below replaces the body of one reference function (cited), is called from pyseqm_b200/_ops.py through
+ * ctypes, and is what a maintainer of the reference would bind instead of the eager-ATen code
+ * (INTEGRATION.md shows the stub).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to caller-owned contiguous memory (PyTorch allocations);
+ *     the library never allocates or frees device memory; scratch is passed in.
+ *   - all floating point data is fp64, index data is int32 unless noted (the int64 index tensors of
+ *     the reference API are narrowed once per geometry by the host layer).
+ *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*), do not synchronise unless
+ *     documented, and keep no global mutable state.
+ *   - return value: 0 on success, negative seqm_status_t otherwise; seqm_last_error() gives the text
+ *     (thread local).
+ *
+ * Layouts
+ *   padded matrices   X[B][n][n], n = 4*S, atom slot a owns rows/cols 4a..4a+3 = (s,px,py,pz)
+ *   block matrices    M[B*S*S][4][4], block index b*S*S + a*S + c  (reference hcore.py:73-158)
+ *   two-centre ints   stored per pair CLASS (HH, XH, XX: hydrogen/heavy), tiles of 32 pairs with the
+ *                     pair index fastest: wXX[tile][100][32], wXH[tile][10][32], wHH[pair]; the packed
+ *                     10x10 index is the reference's (k on atom i)*10 + (l on atom j), fock.py:76-91.
+ *                     seqm_w_expand() materialises the reference's dense w[P][10][10].
+ */
+#ifndef SEQM_B200_H
+#define SEQM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  SEQM_OK = 0,
+  SEQM_EINVAL = -1,      /* bad argument (null pointer, negative size, unsupported size) */
+  SEQM_EUNSUPPORTED = -2,/* element / method / size outside the supported range */
+  SEQM_ECUDA = -3        /* a CUDA runtime call or launch failed */
+} seqm_status_t;
+
+#define SEQM_CLS_HH 0
+#define SEQM_CLS_XH 1
+#define SEQM_CLS_XX 2
+
+/* Pair/atom topology of one batch: the Parser's index tensors (reference basics.py:43-118) narrowed to
+ * int32 plus the CSR tables the no-atomics reductions use. */
+typedef struct {
+  int64_t nmol, molsize, natoms, npairs;
+  const int32_t* Z;          /* [A] atomic number */
+  const int32_t* atom_mol;   /* [A] molecule of the atom */
+  const int32_t* atom_slot;  /* [A] slot in its molecule: maskd = mol*S*S + slot*(S+1) */
+  const int32_t* idxi;       /* [P] first atom of the pair (index into the real-atom list) */
+  const int32_t* idxj;       /* [P] second atom */
+  const int32_t* pair_cls;   /* [P] SEQM_CLS_* */
+  const int32_t* pair_slot;  /* [P] position of the pair inside its class list */
+  const int32_t* cls_pairs[3]; /* [ncls[c]] pair ids of each class, ascending */
+  int64_t ncls[3];
+  const int32_t* start_i;    /* [A+1] pairs whose first atom is a: [start_i[a], start_i[a+1]) */
+  const int32_t* start_j;    /* [A+1] range in perm_j of the pairs whose second atom is a */
+  const int32_t* perm_j;     /* [P] pair ids ordered by second atom */
+} seqm_topology_t;
+
+/* Two-centre integrals in class-tiled storage. */
+typedef struct {
+  double* wHH; /* [ncls[HH]] */
+  double* wXH; /* [ceil(ncls[XH]/32)][10][32] */
+  double* wXX; /* [ceil(ncls[XX]/32)][100][32] */
+} seqm_w_t;
+
+const char* seqm_last_error(void);
+int seqm_version(void);
+size_t seqm_atompar_bytes(void); /* size of one packed per-atom record (seqm_atom_pack output) */
+
+/* Per-atom parameter record: Slater exponents, beta, the point-charge multipole parameters
+ * dd, qq, rho0, rho1, rho2 (reference two_elec_two_center_int.py:7-52, cal_par.py:8-173), core-repulsion
+ * parameters.  gK/gL/gM are [A][ngauss] row-major or NULL when ngauss == 0. */
+int seqm_atom_pack(int64_t natoms, const int32_t* Z, const double* zeta_s, const double* zeta_p,
+                   const double* beta_s, const double* beta_p, const double* g_ss, const double* g_pp,
+                   const double* g_p2, const double* h_sp, const double* alpha, const double* gK,
+                   const double* gL, const double* gM, int ngauss, void* atompar_out, void* stream);
+
+/* hcore() (reference hcore.py:6-167) = two-centre integrals + rotate + diatomic overlap + core
+ * Hamiltonian, and pair_nuclear_energy() (energy.py:38-78).
+ *   xij[P][3], rij[P]      Parser geometry (unit vector i->j, distance in bohr)
+ *   w                      class-tiled integrals (out)
+ *   M[B*S*S][16]           block core Hamiltonian (out; must be zero-filled by the caller: only the upper
+ *                          triangle blocks / upper triangle of diagonal blocks are written)
+ *   EnucAB[P]              core-core repulsion per pair (out, may be NULL)
+ *   pairvec[P][20]         scratch */
+int seqm_hcore(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
+               const double* U_ss, const double* U_pp, int ngauss, seqm_w_t w, double* M, double* EnucAB,
+               double* pairvec, void* stream);
+
+/* dense w[P][10][10] of the reference API from the class-tiled storage */
+int seqm_w_expand(const seqm_topology_t* topo, seqm_w_t w, double* w_dense, void* stream);
+
+/* fock() (reference fock.py:6-139) and elec_energy() (energy.py:19-36).
+ *   P[B][n][n] density, M block core Hamiltonian, F[B][n][n] (out, full symmetric; must have been zero
+ *   filled once by the caller: entries outside the pair pattern are never written)
+ *   active[B] (may be NULL): molecules with active[b]==0 are skipped (frozen once converged)
+ *   Eelec[B] (may be NULL): 0.5*sum P.(Hcore+F) for the active molecules */
+int seqm_fock(const seqm_topology_t* topo, seqm_w_t w, const double* P, const double* M,
+              const double* g_ss, const double* g_pp, const double* g_sp, const double* g_p2,
+              const double* h_sp, const uint8_t* active, double* F, double* Eelec, double* pairvec,
+              void* stream);
+
+/* elec_energy() alone: E[b] = 0.5 * sum_ij P_ij (H_ij + F_ij) with H the symmetrised block matrix M.
+ * xl != 0: XL-BOMD shadow energy  sum D.F - 0.5 (F-H).P  (reference XLBOMD.py:40-52), D given. */
+int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
+                     const double* D, int xl, const uint8_t* active, double* E, void* stream);
+
+/* sym_eig_trunc() (reference diag.py:102-172) with pack/unpack (pack.py:7-41) folded in: batched
+ * symmetric eigensolver on the packed matrix (heavy atoms 4 orbitals, hydrogens 1) and
+ * P = 2 C_occ C_occ^T written back in padded layout.  One CTA per molecule, cyclic Jacobi in shared
+ * memory; supports packed size m <= seqm_eigh_max_m().
+ *   nheavy,nhydro,nocc [B] int32;  e_out[B][n] (may be NULL) ascending orbital energies, zero padded;
+ *   v_out[B][n][n] (may be NULL) eigenvectors in the reference's packed layout C[packed orbital][k];
+ *   info[B] (may be NULL) sweeps used. */
+int seqm_eigh_max_m(void);
+int seqm_eigh_density(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy,
+                      const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
+                      double* e_out, double* v_out, int32_t* info, void* stream);
+
+/* SP2() (reference SP2.py:3-72) on packed matrices with pack/unpack folded in.  Fpad[B][n][n] in,
+ * D[B][n][n] out (= 2 X, padded layout).  work: seqm_sp2_workspace(...) bytes of scratch.
+ * niter[B] (may be NULL) multiplications used.  Synchronises the stream (host reads a counter). */
+size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize);
+int seqm_sp2_density(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy,
+                     const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
+                     double* D, int32_t* niter, void* work, void* stream);
+
+/* The SCF driver: scf_forward0/1/2 (reference scf_loop.py:32-510) run device resident.
+ *   converger: 0 constant mixing (alpha), 1 adaptive, 2 adaptive then Pulay
+ *   P[B][n][n] in: initial guess, out: converged density; F out: fock(P) at the final density
+ *   notconverged[B] out; niter[B] out (iterations taken by each molecule)
+ *   work: seqm_scf_workspace(...) bytes.  Synchronises the stream once per iteration (convergence
+ *   count), like the reference's notconverged.any(). */
+typedef struct {
+  int converger;      /* 0, 1, 2 */
+  double alpha;       /* converger 0 */
+  int use_sp2;        /* density from SP2 instead of eigh */
+  double sp2_eps;
+  double eps;         /* |dEelec| threshold, eV */
+  int max_iter;
+  int debug;          /* print "scf k max_err n_notconverged" like scf_loop.debug */
+} seqm_scf_options_t;
+size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);
+int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss,
+             const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
+             const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc,
+             const seqm_scf_options_t* opt, double* P, double* F, double* Eelec, uint8_t* notconverged,
+             int32_t* niter, double* pairvec, void* work, int32_t* iterations_out, void* stream);
+
+/* Adjoint of hcore + fock + elec_energy + pair_nuclear_energy at fixed density (what autograd replays in
+ * the reference: basics.py:369-388, XLBOMD.py:203-217).
+ *   E = sum_b gE[b]*Eelec_b + sum_p gNuc[p]*EnucAB_p ;  D == NULL: Eelec = 0.5 sum P.(H+F(P)),
+ *   D != NULL (XL-BOMD): Eelec = sum D.F(P) - 0.5 (F(P)-H).P.
+ *   out: grad_xij[P][3], grad_rij[P]  (dE/dxij, dE/drij; chained through the Parser by autograd) */
+int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
+                   int ngauss, const double* P, const double* D, const double* gE, const double* gNuc,
+                   double* grad_xij, double* grad_rij, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,453 @@
+// K0/K1/K4: per-atom parameter packing, the pair pass (two-centre integrals + rotation + overlap + core
+// Hamiltonian + core repulsion) and its adjoint.  One thread per atom pair inside a pair CLASS
+// (HH / XH / XX), so a warp never diverges on the pair type, and the integrals are stored with the pair
+// index fastest ([tile][element][32]) so every global access of the warp is one 256-byte line.
+//
+// reference: seqm/seqm_functions/hcore.py:6-167, two_elec_two_center_int.py:7-878,
+//            two_elec_two_center_int_local_frame.py:18-281, diat_overlap.py:3-393, cal_par.py:8-173,
+//            energy.py:38-78; adjoint = what autograd replays for basics.py:369-388.
+#include "abi_common.cuh"
+#include "pair_math.cuh"
+
+namespace seqm {
+
+thread_local std::string g_last_error;
+void set_error(const std::string& s) { g_last_error = s; }
+
+__constant__ double c_tore[19] = {0, 1, 0, 1, 2, 3, 4, 5, 6, 7, 0, 1, 2, 3, 4, 5, 6, 7, 0};
+__constant__ double c_qn[19] = {0, 1, 0, 2, 2, 2, 2, 2, 2, 2, 0, 3, 3, 3, 3, 3, 3, 3, 0};
+
+// packed index k -> (m, n), m >= n ; IND(mu,nu) -> k
+#define KM(k) ((k) == 0 ? 0 : ((k) <= 2 ? 1 : ((k) <= 5 ? 2 : 3)))
+#define KN(k) ((k) - KM(k) * (KM(k) + 1) / 2)
+#define IND(a, b) ((a) >= (b) ? (a) * ((a) + 1) / 2 + (b) : (b) * ((b) + 1) / 2 + (a))
+#define WT(k) ((KM(k) == KN(k)) ? 1.0 : 2.0)
+
+// ---------------------------------------------------------------------------------------------
+// K0: per-atom record.  rho1/rho2 by the secant iteration of cal_par.py:51-75,138-159.
+// ---------------------------------------------------------------------------------------------
+template <class Fn>
+__device__ double secant_solve(Fn fun, double target, double x1) {
+  double x2 = x1 + 0.04;
+  for (int it = 0; it < 19; ++it) {
+    const double f1 = fun(x1), f2 = fun(x2);
+    const double x3 = (fabs(f2 - f1) > 1.0e-16) ? x1 + (x2 - x1) * (target - f1) / (f2 - f1) : x2;
+    x1 = x2;
+    x2 = x3;
+    if (fabs(fun(x2) - target) < 1.0e-16) break;
+  }
+  return x2;
+}
+
+__global__ void atom_pack_kernel(int natoms, const int32_t* __restrict__ Z, const double* __restrict__ zs,
+                                 const double* __restrict__ zp, const double* __restrict__ bs,
+                                 const double* __restrict__ bp, const double* __restrict__ gss,
+                                 const double* __restrict__ gpp, const double* __restrict__ gp2,
+                                 const double* __restrict__ hsp, const double* __restrict__ alpha,
+                                 const double* __restrict__ gK, const double* __restrict__ gL,
+                                 const double* __restrict__ gM, int ngauss, AtomPar* __restrict__ out) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= natoms) return;
+  const int z = Z[a];
+  AtomPar r;
+  r.zs = zs[a]; r.zp = zp[a]; r.bs = bs[a]; r.bp = bp[a];
+  r.alpha = alpha[a];
+  r.tore = (z >= 0 && z < 19) ? c_tore[z] : 0.0;
+  r.zs15 = r.zs * sqrt(r.zs);
+  r.zs25 = r.zs15 * r.zs;
+  r.zp25 = r.zp * r.zp * sqrt(r.zp);
+  for (int k = 0; k < 4; ++k) {
+    const bool on = k < ngauss;
+    r.gK[k] = on ? gK[a * ngauss + k] : 0.0;
+    r.gL[k] = on ? gL[a * ngauss + k] : 0.0;
+    r.gM[k] = on ? gM[a * ngauss + k] : 0.0;
+  }
+  r.pad_[0] = r.pad_[1] = 0.0;
+  r.mp.dd = r.mp.qq = r.mp.rho0 = r.mp.rho1 = r.mp.rho2 = 0.0;
+  if (z == 1 || z > 2) r.mp.rho0 = 0.5 * SEQM_EV / gss[a];
+  if (z > 2) {
+    const double n = c_qn[z < 19 ? z : 0];
+    const double D1 = (2.0 * n + 1.0) * pow(4.0 * r.zs * r.zp, n + 0.5) / pow(r.zs + r.zp, 2.0 * n + 2.0) /
+                      sqrt(3.0);
+    const double D2 = sqrt((4.0 * n * n + 6.0 * n + 2.0) / 20.0) / r.zp;
+    r.mp.dd = D1;
+    r.mp.qq = D2;
+    const double h1 = hsp[a] / SEQM_EV;
+    double g1 = pow(fabs(h1) / (D1 * D1), 1.0 / 3.0);
+    if (h1 < 0.0) g1 = -g1;
+    const double d = secant_solve(
+        [D1](double x) { return 0.5 * x - 0.5 / sqrt(4.0 * D1 * D1 + 1.0 / (x * x)); }, h1, g1);
+    r.mp.rho1 = 0.5 / d;
+    const double h2 = 0.5 * (gpp[a] - gp2[a]) / SEQM_EV;
+    double g2 = pow(fabs(h2) / 3.0 / (D2 * D2 * D2 * D2), 0.2);
+    if (h2 < 0.0) g2 = -g2;
+    const double q = secant_solve(
+        [D2](double x) {
+          return 0.25 * x - 0.5 / sqrt(4.0 * D2 * D2 + 1.0 / (x * x)) + 0.25 / sqrt(8.0 * D2 * D2 + 1.0 / (x * x));
+        },
+        h2, g2);
+    r.mp.rho2 = 0.5 / q;
+  }
+  out[a] = r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: the pair pass
+// ---------------------------------------------------------------------------------------------
+template <int NELEM>
+struct StoreSink {
+  double* w;       // class storage, already offset to this pair's lane
+  double* pv;      // pairvec row of this pair
+  __device__ __forceinline__ void operator()(int k, int l, double v) const {
+    if (NELEM == 100) w[(size_t)(k * 10 + l) * 32] = v;
+    else if (NELEM == 10) w[(size_t)k * 32] = v;
+    else w[0] = v;
+    if (l == 0) pv[k] = v;
+    if (k == 0) pv[10 + l] = v;
+  }
+};
+
+template <int CLS>
+__global__ void __launch_bounds__(128)
+pair_fwd_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                const double* __restrict__ rij, int ngauss, double* __restrict__ wc, double* __restrict__ M,
+                double* __restrict__ Enuc, double* __restrict__ pairvec) {
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= t.ncls[CLS]) return;
+  const int p = t.cls_pairs[CLS][slot];
+  const int i = t.idxi[p], j = t.idxj[p];
+  const AtomPar& a = ap[i];
+  const AtomPar& b = ap[j];
+  const double x[3] = {xij[3 * p], xij[3 * p + 1], xij[3 * p + 2]};
+  const double r = rij[p];
+  double* pv = pairvec + (size_t)p * 20;
+  double gam;
+  if (CLS == SEQM_CLS_XX) {
+    double ri[22], R[3][3];
+    repp_xx(r, a.mp, b.mp, ri);
+    local_frame(x, R);
+    StoreSink<100> sink{wc + ((size_t)(slot >> 5) * 100) * 32 + (slot & 31), pv};
+    rotate_xx(ri, R, sink);
+    gam = ri[0];
+  } else if (CLS == SEQM_CLS_XH) {
+    double ri[4], R[3][3];
+    repp_xh(r, a.mp, b.mp, ri);
+    local_frame(x, R);
+    StoreSink<10> sink{wc + ((size_t)(slot >> 5) * 10) * 32 + (slot & 31), pv};
+    rotate_xh(ri, R, sink);
+    gam = ri[0];
+  } else {
+    double ri[1];
+    repp_hh(r, a.mp, b.mp, ri);
+    wc[slot] = ri[0];
+    pv[0] = ri[0];
+    pv[10] = ri[0];
+    gam = ri[0];
+  }
+  // resonance block  M[mask] = di * (beta_i + beta_j)/2   (hcore.py:132-149)
+  double di[16];
+  if (r <= SEQM_OVERLAP_CUTOFF) {
+    overlap_block(CLS, x, r, a, b, di);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) di[q] = 0.0;
+  }
+  const int S = (int)t.molsize;
+  const size_t blk = ((size_t)t.atom_mol[i] * S + t.atom_slot[i]) * S + t.atom_slot[j];
+  double* Mb = M + blk * 16;
+#pragma unroll
+  for (int mu = 0; mu < 4; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < 4; ++nu)
+      Mb[mu * 4 + nu] = di[mu * 4 + nu] * 0.5 * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp));
+  if (Enuc) Enuc[p] = core_repulsion(t.Z[i], t.Z[j], r, gam, a, b, ngauss);
+}
+
+// diagonal blocks: U_ss/U_pp + sum over partners of the electron-core attraction, one warp per atom,
+// fixed summation order (no atomics): e1b = -Z'_j w[k][0], e2a = -Z'_i w[0][k]
+__global__ void __launch_bounds__(256)
+hcore_diag_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ pairvec,
+                  const double* __restrict__ Uss, const double* __restrict__ Upp, double* __restrict__ M) {
+  const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (a >= t.natoms) return;
+  const bool heavy = t.Z[a] > 1;
+  double acc[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) acc[k] = 0.0;
+  for (int q = t.start_i[a] + lane; q < t.start_i[a + 1]; q += 32) {
+    const double tj = ap[t.idxj[q]].tore;
+    const double* pv = pairvec + (size_t)q * 20;
+    acc[0] -= tj * pv[0];
+    if (heavy) {
+#pragma unroll
+      for (int k = 1; k < 10; ++k) acc[k] -= tj * pv[k];
+    }
+  }
+  for (int q = t.start_j[a] + lane; q < t.start_j[a + 1]; q += 32) {
+    const int p = t.perm_j[q];
+    const double ti = ap[t.idxi[p]].tore;
+    const double* pv = pairvec + (size_t)p * 20 + 10;
+    acc[0] -= ti * pv[0];
+    if (heavy) {
+#pragma unroll
+      for (int k = 1; k < 10; ++k) acc[k] -= ti * pv[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 10; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+  }
+  if (lane == 0) {
+    const int S = (int)t.molsize;
+    double* Mb = M + (((size_t)t.atom_mol[a] * S + t.atom_slot[a]) * S + t.atom_slot[a]) * 16;
+    const double us = Uss[a], up = Upp[a];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+      const int m = KM(k), n = KN(k);
+      double v = acc[k];
+      if (k == 0) v += us;
+      else if (m == n) v += up;
+      Mb[n * 4 + m] = v;
+    }
+  }
+}
+
+__global__ void w_expand_kernel(seqm_topology_t t, seqm_w_t w, double* __restrict__ out) {
+  const long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= (long long)t.npairs * 100) return;
+  const int p = (int)(id / 100), e = (int)(id % 100);
+  const int cls = t.pair_cls[p], slot = t.pair_slot[p];
+  double v = 0.0;
+  if (cls == SEQM_CLS_XX) v = w.wXX[wtile_index(slot, e, 100)];
+  else if (cls == SEQM_CLS_XH) { if (e % 10 == 0) v = w.wXH[wtile_index(slot, e / 10, 10)]; }
+  else { if (e == 0) v = w.wHH[slot]; }
+  out[id] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4: adjoint of the pair pass at fixed density.  Forward-mode duals over (x1,x2,x3,r) through the very
+// same templated functions (identical branches), contracted on the fly with the closed-form upstream
+//   dE/dw[k][l] = qA_k pB_l + pA_k qB_l - sum Q_AB[mu][lam] P_AB[nu][sig]   (+ core attraction terms)
+//   dE/dM_AB    = 2 X_AB,  with (X,Q) = (P, P/2) for the SCF energy and (D, D - P/2) for XL-BOMD.
+// ---------------------------------------------------------------------------------------------
+typedef Dual<4> D4;
+
+template <int NELEM>
+struct DotSink {
+  const double* G;   // upstream dE/dw of this pair (local array)
+  D4 acc;
+  D4 w00;
+  __device__ __forceinline__ void operator()(int k, int l, const D4& v) {
+    const double g = (NELEM == 100) ? G[k * 10 + l] : G[k];
+    acc.v += g * v.v;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc.d[q] += g * v.d[q];
+    if (k == 0 && l == 0) w00 = v;
+  }
+};
+
+__device__ __forceinline__ void load_diag_packed(const double* __restrict__ X, size_t n4, int slot, double* out) {
+  // weighted packed upper triangle of the atom's diagonal block: wt * X[n][m], k = (m,n)
+  const double* base = X + ((size_t)4 * slot) * n4 + 4 * slot;
+#pragma unroll
+  for (int k = 0; k < 10; ++k) out[k] = WT(k) * base[(size_t)KN(k) * n4 + KM(k)];
+}
+
+template <int CLS>
+__global__ void __launch_bounds__(128)
+pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                 const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                 const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
+                 double* __restrict__ gx, double* __restrict__ gr) {
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= t.ncls[CLS]) return;
+  const int p = t.cls_pairs[CLS][slot];
+  const int i = t.idxi[p], j = t.idxj[p];
+  const AtomPar& a = ap[i];
+  const AtomPar& b = ap[j];
+  const int S = (int)t.molsize;
+  const size_t n4 = (size_t)4 * S;
+  const int mol = t.atom_mol[i];
+  const int si = t.atom_slot[i], sj = t.atom_slot[j];
+  const double* Pm = P + (size_t)mol * n4 * n4;
+  const double* Dmm = Dm ? Dm + (size_t)mol * n4 * n4 : nullptr;
+  constexpr int NA = (CLS == SEQM_CLS_HH) ? 1 : 10;     // products that exist on atom i
+  constexpr int NB = (CLS == SEQM_CLS_XX) ? 10 : 1;     // ... on atom j
+  constexpr int OA = (CLS == SEQM_CLS_HH) ? 1 : 4;      // orbitals on atom i
+  constexpr int OB = (CLS == SEQM_CLS_XX) ? 4 : 1;
+  double pA[10], pB[10], qA[10], qB[10], xA[10], xB[10];
+  load_diag_packed(Pm, n4, si, pA);
+  load_diag_packed(Pm, n4, sj, pB);
+  if (Dmm) {
+    load_diag_packed(Dmm, n4, si, xA);
+    load_diag_packed(Dmm, n4, sj, xB);
+#pragma unroll
+    for (int k = 0; k < 10; ++k) { qA[k] = xA[k] - 0.5 * pA[k]; qB[k] = xB[k] - 0.5 * pB[k]; }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 10; ++k) { xA[k] = pA[k]; xB[k] = pB[k]; qA[k] = 0.5 * pA[k]; qB[k] = 0.5 * pB[k]; }
+  }
+  double Pab[4][4], Qab[4][4], Xab[4][4];
+#pragma unroll
+  for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < OB; ++nu) {
+      const size_t off = ((size_t)4 * si + mu) * n4 + 4 * sj + nu;
+      const double pv = Pm[off];
+      Pab[mu][nu] = pv;
+      if (Dmm) { const double dv = Dmm[off]; Xab[mu][nu] = dv; Qab[mu][nu] = dv - 0.5 * pv; }
+      else { Xab[mu][nu] = pv; Qab[mu][nu] = 0.5 * pv; }
+    }
+  // upstream on the integrals
+  double G[NA * NB];
+#pragma unroll
+  for (int k = 0; k < NA; ++k)
+#pragma unroll
+    for (int l = 0; l < NB; ++l) G[k * NB + l] = qA[k] * pB[l] + pA[k] * qB[l];
+#pragma unroll
+  for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < OA; ++nu)
+#pragma unroll
+      for (int la = 0; la < OB; ++la)
+#pragma unroll
+        for (int sg = 0; sg < OB; ++sg) G[IND(mu, nu) * NB + IND(la, sg)] -= Qab[mu][la] * Pab[nu][sg];
+#pragma unroll
+  for (int k = 0; k < NA; ++k) G[k * NB] -= b.tore * xA[k];
+#pragma unroll
+  for (int l = 0; l < NB; ++l) G[l] -= a.tore * xB[l];
+
+  D4 x[3], r;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { x[c] = D4(xij[3 * p + c]); x[c].d[c] = 1.0; }
+  r = D4(rij[p]);
+  r.d[3] = 1.0;
+
+  D4 eel(0.0), gam;
+  if (CLS == SEQM_CLS_XX) {
+    D4 ri[22], R[3][3];
+    repp_xx(r, a.mp, b.mp, ri);
+    local_frame(x, R);
+    DotSink<100> sink{G, D4(0.0), D4(0.0)};
+    rotate_xx(ri, R, sink);
+    eel = sink.acc; gam = sink.w00;
+  } else if (CLS == SEQM_CLS_XH) {
+    D4 ri[4], R[3][3];
+    repp_xh(r, a.mp, b.mp, ri);
+    local_frame(x, R);
+    DotSink<10> sink{G, D4(0.0), D4(0.0)};
+    rotate_xh(ri, R, sink);
+    eel = sink.acc; gam = sink.w00;
+  } else {
+    D4 ri[1];
+    repp_hh(r, a.mp, b.mp, ri);
+    eel = ri[0] * G[0];
+    gam = ri[0];
+  }
+  if (rij[p] <= SEQM_OVERLAP_CUTOFF) {
+    D4 di[16];
+    overlap_block(CLS, x, r, a, b, di);
+#pragma unroll
+    for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+      for (int nu = 0; nu < OB; ++nu)
+        eel = eel + di[mu * 4 + nu] * (Xab[mu][nu] * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp)));
+  }
+  const double ge = gE ? gE[mol] : 1.0;
+  const double gn = gNuc ? gNuc[p] : 1.0;
+  const D4 en = core_repulsion(t.Z[i], t.Z[j], r, gam, a, b, ngauss);
+  gx[3 * p + 0] = ge * eel.d[0] + gn * en.d[0];
+  gx[3 * p + 1] = ge * eel.d[1] + gn * en.d[1];
+  gx[3 * p + 2] = ge * eel.d[2] + gn * en.d[2];
+  gr[p] = ge * eel.d[3] + gn * en.d[3];
+}
+
+}  // namespace seqm
+
+using namespace seqm;
+
+extern "C" {
+
+const char* seqm_last_error(void) { return g_last_error.c_str(); }
+int seqm_version(void) { return 100; }
+size_t seqm_atompar_bytes(void) { return sizeof(AtomPar); }
+
+int seqm_atom_pack(int64_t natoms, const int32_t* Z, const double* zeta_s, const double* zeta_p,
+                   const double* beta_s, const double* beta_p, const double* g_ss, const double* g_pp,
+                   const double* g_p2, const double* h_sp, const double* alpha, const double* gK,
+                   const double* gL, const double* gM, int ngauss, void* atompar_out, void* stream) {
+  SEQM_REQUIRE(natoms >= 0 && ngauss >= 0 && ngauss <= 4, "seqm_atom_pack: bad sizes");
+  SEQM_REQUIRE(Z && zeta_s && zeta_p && beta_s && beta_p && g_ss && g_pp && g_p2 && h_sp && alpha && atompar_out,
+               "seqm_atom_pack: null pointer");
+  SEQM_REQUIRE(ngauss == 0 || (gK && gL && gM), "seqm_atom_pack: gaussians missing");
+  if (natoms == 0) return SEQM_OK;
+  atom_pack_kernel<<<cdiv(natoms, 128), 128, 0, (cudaStream_t)stream>>>(
+      (int)natoms, Z, zeta_s, zeta_p, beta_s, beta_p, g_ss, g_pp, g_p2, h_sp, alpha, gK, gL, gM, ngauss,
+      (AtomPar*)atompar_out);
+  SEQM_CHECK_LAUNCH("atom_pack_kernel");
+  return SEQM_OK;
+}
+
+int seqm_hcore(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
+               const double* U_ss, const double* U_pp, int ngauss, seqm_w_t w, double* M, double* EnucAB,
+               double* pairvec, void* stream) {
+  SEQM_REQUIRE(topo && atompar && xij && rij && U_ss && U_pp && M && pairvec, "seqm_hcore: null pointer");
+  SEQM_REQUIRE(ngauss >= 0 && ngauss <= 4, "seqm_hcore: ngauss");
+  const seqm_topology_t& t = *topo;
+  cudaStream_t st = (cudaStream_t)stream;
+  const AtomPar* ap = (const AtomPar*)atompar;
+  if (t.ncls[SEQM_CLS_XX] > 0) {
+    SEQM_REQUIRE(w.wXX, "seqm_hcore: wXX null");
+    pair_fwd_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wXX, M, EnucAB, pairvec);
+    SEQM_CHECK_LAUNCH("pair_fwd_kernel<XX>");
+  }
+  if (t.ncls[SEQM_CLS_XH] > 0) {
+    SEQM_REQUIRE(w.wXH, "seqm_hcore: wXH null");
+    pair_fwd_kernel<SEQM_CLS_XH><<<cdiv(t.ncls[1], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wXH, M, EnucAB, pairvec);
+    SEQM_CHECK_LAUNCH("pair_fwd_kernel<XH>");
+  }
+  if (t.ncls[SEQM_CLS_HH] > 0) {
+    SEQM_REQUIRE(w.wHH, "seqm_hcore: wHH null");
+    pair_fwd_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wHH, M, EnucAB, pairvec);
+    SEQM_CHECK_LAUNCH("pair_fwd_kernel<HH>");
+  }
+  if (t.natoms > 0) {
+    hcore_diag_kernel<<<cdiv(t.natoms * 32, 256), 256, 0, st>>>(t, ap, pairvec, U_ss, U_pp, M);
+    SEQM_CHECK_LAUNCH("hcore_diag_kernel");
+  }
+  return SEQM_OK;
+}
+
+int seqm_w_expand(const seqm_topology_t* topo, seqm_w_t w, double* w_dense, void* stream) {
+  SEQM_REQUIRE(topo && w_dense, "seqm_w_expand: null pointer");
+  if (topo->npairs == 0) return SEQM_OK;
+  w_expand_kernel<<<cdiv(topo->npairs * 100, 256), 256, 0, (cudaStream_t)stream>>>(*topo, w, w_dense);
+  SEQM_CHECK_LAUNCH("w_expand_kernel");
+  return SEQM_OK;
+}
+
+int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
+                   int ngauss, const double* P, const double* D, const double* gE, const double* gNuc,
+                   double* grad_xij, double* grad_rij, void* stream) {
+  SEQM_REQUIRE(topo && atompar && xij && rij && P && grad_xij && grad_rij, "seqm_pair_grad: null pointer");
+  const seqm_topology_t& t = *topo;
+  cudaStream_t st = (cudaStream_t)stream;
+  const AtomPar* ap = (const AtomPar*)atompar;
+  if (t.ncls[2] > 0) {
+    pair_grad_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
+    SEQM_CHECK_LAUNCH("pair_grad_kernel<XX>");
+  }
+  if (t.ncls[1] > 0) {
+    pair_grad_kernel<SEQM_CLS_XH><<<cdiv(t.ncls[1], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
+    SEQM_CHECK_LAUNCH("pair_grad_kernel<XH>");
+  }
+  if (t.ncls[0] > 0) {
+    pair_grad_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
+    SEQM_CHECK_LAUNCH("pair_grad_kernel<HH>");
+  }
+  return SEQM_OK;
+}
+
+}  // extern "C"
