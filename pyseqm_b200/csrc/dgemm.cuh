@@ -1,0 +1,21 @@
+// internal cross-file declarations of the seqm_b200 library
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "../../include/seqm_b200.h"
+
+namespace seqm {
+
+int launch_dgemm_batched(int n, int ld, const double* A, const double* B, double* C, long long stride, int batch,
+                         const uint8_t* active, const int32_t* dims, cudaStream_t st);
+
+int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const double* M, const double* g_ss,
+                const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
+                const uint8_t* active, double* F, double* Eelec, double* pairvec, cudaStream_t st);
+
+int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                        const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
+                        double* e_out, double* v_out, int32_t* info, cudaStream_t st);
+
+}  // namespace seqm

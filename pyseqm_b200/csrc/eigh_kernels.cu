@@ -1,0 +1,215 @@
+// K3a: batched symmetric eigensolver + density, one CTA per molecule, everything in shared memory.
+//   pack (pack.py:7-21) -> parallel-order cyclic Jacobi (two-sided, tournament schedule: every round
+//   rotates m/2 disjoint index pairs, each thread owns 2x2 tiles so a round needs two barriers) ->
+//   rank sort of the eigenvalues -> P = 2 C_occ C_occ^T -> unpack (pack.py:34-41) to the padded layout.
+// Works on the PACKED matrix (m = 4 nHeavy + nHydro), so the reference's trick of pushing the padding
+// rows above the spectrum (diag.py:116-130) is not needed; orbital energies are returned zero padded like
+// diag.py:140-144.
+// reference: seqm/seqm_functions/diag.py:102-172
+#include "abi_common.cuh"
+
+namespace seqm {
+
+constexpr int EIGH_MAX_M = 118;
+constexpr int EIGH_MAX_SWEEPS = 40;
+
+__device__ __forceinline__ int packed_to_padded(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
+
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double s = 0.0;
+  const int nw = (blockDim.x + 31) >> 5;
+  for (int q = 0; q < nw; ++q) s += red[q];
+  return s;
+}
+
+__global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
+                                    const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
+                                    const uint8_t* __restrict__ active, double* __restrict__ P,
+                                    double* __restrict__ e_out, double* __restrict__ v_out,
+                                    int32_t* __restrict__ info) {
+  const int mol = blockIdx.x;
+  if (active && !active[mol]) return;
+  const int nh4 = 4 * nheavy[mol];
+  const int m = nh4 + nhydro[mol];
+  const int n4 = 4 * S;
+  const size_t base = (size_t)mol * n4 * n4;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  if (m <= 0) return;
+  const int mp = (m + 1) & ~1;      // even size for the tournament; the extra index never couples
+  const int ld = mp + 1;
+  extern __shared__ double sm[];
+  double* A = sm;                          // [mp][ld]
+  double* V = A + (size_t)ldmax * (ldmax + 1);   // [mp][ld]
+  double* cs = V + (size_t)ldmax * (ldmax + 1);  // [mp/2][2]
+  double* red = cs + ldmax;                // [32]
+  int* pq = (int*)(red + 32);              // [mp/2][2]
+  int* rank = pq + ldmax;                  // [mp]
+  int* occ = rank + ldmax;                 // [mp]
+
+  for (int idx = tid; idx < mp * mp; idx += nt) {
+    const int i = idx / mp, j = idx - i * mp;
+    double a = 0.0;
+    if (i < m && j < m) {
+      const int r = i <= j ? i : j, c = i <= j ? j : i;     // upper triangle, like eigh(UPLO='U')
+      a = F[base + (size_t)packed_to_padded(r, nh4) * n4 + packed_to_padded(c, nh4)];
+    }
+    A[i * ld + j] = a;
+    V[i * ld + j] = (i == j) ? 1.0 : 0.0;
+  }
+  __syncthreads();
+
+  const int half = mp >> 1;
+  int sweeps = 0;
+  bool last = false;
+  for (; sweeps < EIGH_MAX_SWEEPS; ++sweeps) {
+    // off-diagonal and total norms
+    double off = 0.0, tot = 0.0;
+    for (int idx = tid; idx < mp * mp; idx += nt) {
+      const int i = idx / mp, j = idx - i * mp;
+      const double a = A[i * ld + j];
+      tot += a * a;
+      if (i != j) off += a * a;
+    }
+    off = block_sum(off, red);
+    tot = block_sum(tot, red);
+    if (off == 0.0 || last) break;
+    if (off <= 1.0e-28 * tot) last = true;      // one more sweep after reaching 1e-14 relative
+    for (int r = 0; r < mp - 1; ++r) {
+      if (tid < half) {
+        int p, q;
+        if (tid == 0) { p = mp - 1; q = r; }
+        else { p = (r + tid) % (mp - 1); q = (r - tid + mp - 1) % (mp - 1); }
+        if (p > q) { const int tmp = p; p = q; q = tmp; }
+        const double apq = A[p * ld + q];
+        double c = 1.0, s = 0.0;
+        if (apq != 0.0) {
+          const double theta = (A[q * ld + q] - A[p * ld + p]) / (2.0 * apq);
+          const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+          c = 1.0 / sqrt(tt * tt + 1.0);
+          s = tt * c;
+        }
+        cs[2 * tid] = c; cs[2 * tid + 1] = s;
+        pq[2 * tid] = p; pq[2 * tid + 1] = q;
+      }
+      __syncthreads();
+      const int nblk = half * half;
+      for (int task = tid; task < nblk + mp * half; task += nt) {
+        if (task < nblk) {
+          const int ka = task / half, kb = task - ka * half;
+          const int pa = pq[2 * ka], qa = pq[2 * ka + 1], pb = pq[2 * kb], qb = pq[2 * kb + 1];
+          const double ca = cs[2 * ka], sa = cs[2 * ka + 1], cb = cs[2 * kb], sb = cs[2 * kb + 1];
+          const double a00 = A[pa * ld + pb], a01 = A[pa * ld + qb], a10 = A[qa * ld + pb], a11 = A[qa * ld + qb];
+          // rows: J_a^T * blk
+          const double b00 = ca * a00 - sa * a10, b01 = ca * a01 - sa * a11;
+          const double b10 = sa * a00 + ca * a10, b11 = sa * a01 + ca * a11;
+          // columns: * J_b
+          double c00 = cb * b00 - sb * b01, c01 = sb * b00 + cb * b01;
+          double c10 = cb * b10 - sb * b11, c11 = sb * b10 + cb * b11;
+          if (ka == kb) { c01 = 0.0; c10 = 0.0; }
+          A[pa * ld + pb] = c00; A[pa * ld + qb] = c01; A[qa * ld + pb] = c10; A[qa * ld + qb] = c11;
+        } else {
+          const int t2 = task - nblk;
+          const int i = t2 / half, kb = t2 - i * half;
+          const int pb = pq[2 * kb], qb = pq[2 * kb + 1];
+          const double cb = cs[2 * kb], sb = cs[2 * kb + 1];
+          const double v0 = V[i * ld + pb], v1 = V[i * ld + qb];
+          V[i * ld + pb] = cb * v0 - sb * v1;
+          V[i * ld + qb] = sb * v0 + cb * v1;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  if (info && tid == 0) info[mol] = sweeps;
+
+  // rank of every eigenvalue (ascending, ties by index: a stable sort)
+  for (int i = tid; i < m; i += nt) {
+    const double ei = A[i * ld + i];
+    int rk = 0;
+    for (int j = 0; j < m; ++j) {
+      const double ej = A[j * ld + j];
+      rk += (ej < ei || (ej == ei && j < i)) ? 1 : 0;
+    }
+    rank[i] = rk;
+  }
+  __syncthreads();
+  const int no = nocc[mol];
+  for (int i = tid; i < m; i += nt) {
+    if (rank[i] < no) occ[rank[i]] = i;
+    if (e_out) e_out[(size_t)mol * n4 + rank[i]] = A[i * ld + i];
+  }
+  if (e_out)
+    for (int i = m + tid; i < n4; i += nt) e_out[(size_t)mol * n4 + i] = 0.0;
+  if (v_out) {
+    // eigenvectors as columns in ascending order, packed rows: v[i][rank]
+    for (int idx = tid; idx < m * m; idx += nt) {
+      const int i = idx / m, k = idx - i * m;
+      v_out[base + (size_t)i * n4 + rank[k]] = V[i * ld + k];
+    }
+  }
+  __syncthreads();
+  // occupied coefficient block C[i][k] into A (the rotated matrix is no longer needed)
+  const int nocc_c = no < m ? no : m;
+  for (int idx = tid; idx < m * nocc_c; idx += nt) {
+    const int i = idx / nocc_c, k = idx - i * nocc_c;
+    A[i * ld + k] = V[i * ld + occ[k]];
+  }
+  __syncthreads();
+  for (int idx = tid; idx < m * m; idx += nt) {
+    const int i = idx / m, j = idx - i * m;
+    const int r = i <= j ? i : j, c = i <= j ? j : i;     // same operand order for (i,j) and (j,i)
+    double acc = 0.0;
+    for (int k = 0; k < nocc_c; ++k) acc += A[r * ld + k] * A[c * ld + k];
+    P[base + (size_t)packed_to_padded(i, nh4) * n4 + packed_to_padded(j, nh4)] = 2.0 * acc;
+  }
+}
+
+size_t eigh_smem_bytes(int mmax) {
+  const int mp = (mmax + 1) & ~1;
+  return ((size_t)2 * mp * (mp + 1) + mp + 32) * sizeof(double) + (size_t)3 * mp * sizeof(int) + 64;
+}
+
+int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                        const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
+                        double* e_out, double* v_out, int32_t* info, cudaStream_t st) {
+  if (nmol == 0) return SEQM_OK;
+  if (mmax > EIGH_MAX_M) return fail(SEQM_EUNSUPPORTED, "seqm_eigh_density: packed size above the shared-memory Jacobi limit (118); use the SP2 density path");
+  if (mmax < 1) mmax = 1;
+  const int mp = (mmax + 1) & ~1;
+  const size_t smem = eigh_smem_bytes(mmax);
+  int threads = ((3 * mp * mp / 4) / 2 + 31) / 32 * 32;
+  if (threads < 64) threads = 64;
+  if (threads > 1024) threads = 1024;
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  eigh_density_kernel<<<(unsigned)nmol, threads, smem, st>>>((int)molsize, mp, F, nheavy, nhydro, nocc, active, P,
+                                                           e_out, v_out, info);
+  SEQM_CHECK_LAUNCH("eigh_density_kernel");
+  return SEQM_OK;
+}
+
+}  // namespace seqm
+
+using namespace seqm;
+
+extern "C" {
+
+int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
+
+int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                      const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
+                      double* v_out, int32_t* info, void* stream) {
+  SEQM_REQUIRE(F && nheavy && nhydro && nocc && P && nmol >= 0 && molsize > 0, "seqm_eigh_density: bad argument");
+  return launch_eigh_density(nmol, molsize, mmax, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info,
+                             (cudaStream_t)stream);
+}
+
+}  // extern "C"

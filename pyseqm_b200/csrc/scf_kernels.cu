@@ -1,0 +1,354 @@
+// K3c: the SCF driver.  scf_forward0 (constant mixing), scf_forward1 (adaptive mixing, MOPAC cnvg) and
+// scf_forward2 (2 direct + 1 adaptive + Pulay/DIIS with a ring of 5 Fock matrices) of the reference, with
+// every per-molecule update masked by the device-resident `notconverged` flags exactly as the reference
+// masks with notconverged[...] — converged molecules are frozen, CTAs assigned to them exit at once.
+// The host loop only reads back one integer (how many molecules are still unconverged) per iteration,
+// the analogue of the reference's notconverged.any().
+// reference: seqm/seqm_functions/scf_loop.py:32-510 (iteration schedule and EMAT/EVEC ring arithmetic,
+// including the stale-lower-triangle quirk after the ring wraps, scf_loop.py:460-490)
+#include <vector>
+
+#include "abi_common.cuh"
+#include "dgemm.cuh"
+
+namespace seqm {
+
+constexpr int NFOCK = 5;
+
+enum MixMode { MIX_DIRECT = 0, MIX_CONST = 1, MIX_ADAPTIVE = 2, MIX_TAKE = 3 };
+
+// one CTA per molecule.  DIRECT: Pold = P, P = Pnew.  CONST: P = alpha P + (1-alpha) Pnew.
+// ADAPTIVE: fac from the padded diagonals, Pold = P, P = (1+fac) Pnew - fac P.  TAKE: P = Pnew.
+__global__ void __launch_bounds__(256)
+mix_kernel(int n4, int mode, double alpha, const uint8_t* __restrict__ active, const double* __restrict__ Pnew,
+           double* __restrict__ P, double* __restrict__ Pold) {
+  const int mol = blockIdx.x;
+  if (active && !active[mol]) return;
+  const size_t base = (size_t)mol * n4 * n4;
+  const int nn = n4 * n4;
+  double fac = 0.0;
+  if (mode == MIX_ADAPTIVE) {
+    __shared__ double red[2][8];
+    double num = 0.0, den = 0.0;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+      const size_t d = base + (size_t)i * n4 + i;
+      const double dn = Pnew[d], dc = P[d], dold = Pold[d];
+      num += (dn - dc) * (dn - dc);
+      const double u = dn - dc * 2.0 + dold;
+      den += u * u;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      num += __shfl_xor_sync(0xffffffffu, num, o);
+      den += __shfl_xor_sync(0xffffffffu, den, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = num; red[1][threadIdx.x >> 5] = den; }
+    __syncthreads();
+    num = 0.0; den = 0.0;
+    for (int q = 0; q < (int)(blockDim.x >> 5); ++q) { num += red[0][q]; den += red[1][q]; }
+    fac = sqrt(num / den);
+  }
+  for (int idx = threadIdx.x; idx < nn; idx += blockDim.x) {
+    const double pn = Pnew[base + idx];
+    const double pc = P[base + idx];
+    if (mode == MIX_DIRECT) { Pold[base + idx] = pc; P[base + idx] = pn; }
+    else if (mode == MIX_CONST) { P[base + idx] = alpha * pc + (1.0 - alpha) * pn; }
+    else if (mode == MIX_ADAPTIVE) { Pold[base + idx] = pc; P[base + idx] = (1.0 + fac) * pn - fac * pc; }
+    else { P[base + idx] = pn; }
+  }
+}
+
+// err = |Enew - E|, E = Enew, niter++, notconverged = err > eps (for the still active molecules);
+// counts the molecules left and tracks max err (as an ordered integer image of the non-negative double)
+__global__ void finish_step_kernel(int nmol, double eps, const double* __restrict__ Enew, double* __restrict__ E,
+                                   double* __restrict__ err, uint8_t* __restrict__ nc, int32_t* __restrict__ niter,
+                                   unsigned long long* __restrict__ stat) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nmol) return;
+  if (nc[b]) {
+    const double en = Enew[b];
+    err[b] = fabs(en - E[b]);
+    E[b] = en;
+    niter[b] += 1;
+  }
+  const double e = err[b];
+  const bool still = e > eps;
+  nc[b] = still ? 1 : 0;
+  if (still) atomicAdd(&stat[0], 1ULL);
+  atomicMax(&stat[1], (unsigned long long)__double_as_longlong(e));
+}
+
+// Pulay store: FOCK[c] = F, FPPF[c] = triu(G - G^T) with G = F P
+__global__ void __launch_bounds__(256)
+pulay_store_kernel(int n4, int slot, const uint8_t* __restrict__ active, const double* __restrict__ F,
+                   const double* __restrict__ G, double* __restrict__ FOCK, double* __restrict__ FPPF) {
+  const int mol = blockIdx.x;
+  if (active && !active[mol]) return;
+  const size_t nn = (size_t)n4 * n4;
+  const size_t src = (size_t)mol * nn;
+  const size_t dst = ((size_t)mol * NFOCK + slot) * nn;
+  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) {
+    const int i = idx / n4, j = idx - i * n4;
+    FOCK[dst + idx] = F[src + idx];
+    FPPF[dst + idx] = (j >= i) ? G[src + idx] - G[src + (size_t)j * n4 + i] : 0.0;
+  }
+}
+
+// EMAT[c][s] = <FPPF[c], FPPF[s]> for s < cF; grid (cF, nmol)
+__global__ void __launch_bounds__(256)
+pulay_emat_kernel(int n4, int slot, const uint8_t* __restrict__ active, const double* __restrict__ FPPF,
+                  double* __restrict__ EMAT) {
+  const int mol = blockIdx.y, s = blockIdx.x;
+  if (active && !active[mol]) return;
+  const size_t nn = (size_t)n4 * n4;
+  const double* a = FPPF + ((size_t)mol * NFOCK + slot) * nn;
+  const double* b = FPPF + ((size_t)mol * NFOCK + s) * nn;
+  double acc = 0.0;
+  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) acc += a[idx] * b[idx];
+  __shared__ double red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int q = 0; q < (int)(blockDim.x >> 5); ++q) t += red[q];
+    EMAT[(size_t)mol * 36 + slot * 6 + s] = t;
+  }
+}
+
+// EVEC = EMAT + tril(EMAT,-1)^T; EVEC[:cF,:cF] /= EVEC[c][c]; coeff = -inverse(EVEC[:cF+1,:cF+1])[:-1,-1];
+// F = sum_s coeff_s FOCK[s]
+__global__ void __launch_bounds__(256)
+pulay_extrapolate_kernel(int n4, int slot, int cF, const uint8_t* __restrict__ active,
+                         const double* __restrict__ EMAT, const double* __restrict__ FOCK, double* __restrict__ F) {
+  const int mol = blockIdx.x;
+  if (active && !active[mol]) return;
+  __shared__ double coeff[NFOCK];
+  if (threadIdx.x == 0) {
+    const double* em = EMAT + (size_t)mol * 36;
+    const int d = cF + 1;
+    double a[6][7];
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) a[i][j] = em[i * 6 + j] + (j > i ? em[j * 6 + i] : 0.0);
+    const double sc = a[slot][slot];
+    for (int i = 0; i < cF; ++i)
+      for (int j = 0; j < cF; ++j) a[i][j] = a[i][j] / sc;
+    // solve a[:d,:d] x = e_{d-1} by Gaussian elimination with partial pivoting: x = last column of the inverse
+    for (int i = 0; i < d; ++i) a[i][6] = (i == d - 1) ? 1.0 : 0.0;
+    for (int c = 0; c < d; ++c) {
+      int piv = c;
+      double best = fabs(a[c][c]);
+      for (int r = c + 1; r < d; ++r)
+        if (fabs(a[r][c]) > best) { best = fabs(a[r][c]); piv = r; }
+      if (piv != c) {
+        for (int j = 0; j < 7; ++j) { const double tmp = a[c][j]; a[c][j] = a[piv][j]; a[piv][j] = tmp; }
+      }
+      const double inv = 1.0 / a[c][c];
+      for (int r = c + 1; r < d; ++r) {
+        const double f = a[r][c] * inv;
+        for (int j = c; j < d; ++j) a[r][j] -= f * a[c][j];
+        a[r][6] -= f * a[c][6];
+      }
+    }
+    double x[6];
+    for (int r = d - 1; r >= 0; --r) {
+      double sum = a[r][6];
+      for (int j = r + 1; j < d; ++j) sum -= a[r][j] * x[j];
+      x[r] = sum / a[r][r];
+    }
+    for (int s = 0; s < cF; ++s) coeff[s] = -x[s];
+  }
+  __syncthreads();
+  const size_t nn = (size_t)n4 * n4;
+  const double* fo = FOCK + (size_t)mol * NFOCK * nn;
+  double* out = F + (size_t)mol * nn;
+  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) {
+    double acc = 0.0;
+    for (int s = 0; s < cF; ++s) acc += fo[(size_t)s * nn + idx] * coeff[s];
+    out[idx] = acc;
+  }
+}
+
+__global__ void init_flags_kernel(int nmol, uint8_t* nc, double* err, int32_t* niter, double* EMAT) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nmol) return;
+  nc[b] = 1;
+  err[b] = 1.0;
+  niter[b] = 0;
+  if (EMAT) {
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) EMAT[(size_t)b * 36 + i * 6 + j] = (i > j) ? -1.0 : 0.0;
+  }
+}
+
+struct ScfWork {
+  double *Pnew, *Pold, *Enew, *err, *G, *FOCK, *FPPF, *EMAT;
+  unsigned long long* stat;
+  char* sp2;
+  size_t total;
+};
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt) {
+  ScfWork w{};
+  const size_t nn = (size_t)16 * molsize * molsize;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align256(bytes); return p; };
+  w.Pnew = (double*)take(nmol * nn * 8);
+  w.Pold = (double*)take(nmol * nn * 8);
+  w.Enew = (double*)take(nmol * 8);
+  w.err = (double*)take(nmol * 8);
+  w.stat = (unsigned long long*)take(64);
+  if (opt->converger == 2) {
+    w.G = (double*)take(nmol * nn * 8);
+    w.FOCK = (double*)take(nmol * NFOCK * nn * 8);
+    w.FPPF = (double*)take(nmol * NFOCK * nn * 8);
+    w.EMAT = (double*)take(nmol * 36 * 8);
+  }
+  if (opt->use_sp2) w.sp2 = take(seqm_sp2_workspace(nmol, molsize));
+  w.total = off;
+  return w;
+}
+
+}  // namespace seqm
+
+using namespace seqm;
+
+extern "C" {
+
+size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt) {
+  if (!opt) return 0;
+  return carve(nullptr, nmol, molsize, opt).total;
+}
+
+int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss, const double* g_pp,
+             const double* g_sp, const double* g_p2, const double* h_sp, const int32_t* nheavy,
+             const int32_t* nhydro, const int32_t* nocc, int mmax, const seqm_scf_options_t* opt, double* P,
+             double* F, double* Eelec, uint8_t* notconverged, int32_t* niter, double* pairvec, void* work,
+             int32_t* iterations_out, void* stream) {
+  SEQM_REQUIRE(topo && M && g_ss && g_pp && g_sp && g_p2 && h_sp && nheavy && nhydro && nocc && opt && P && F &&
+                   Eelec && notconverged && niter && pairvec && work,
+               "seqm_scf: null pointer");
+  SEQM_REQUIRE(opt->converger >= 0 && opt->converger <= 2, "seqm_scf: scf_converger must be [0, alpha], [1] or [2]");
+  const seqm_topology_t& t = *topo;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = (int)t.nmol, S = (int)t.molsize, n4 = 4 * S;
+  const size_t nn = (size_t)n4 * n4;
+  if (B == 0) { if (iterations_out) *iterations_out = 0; return SEQM_OK; }
+  ScfWork wk = carve((char*)work, B, S, opt);
+  uint8_t* nc = notconverged;
+  int rc;
+
+  SEQM_CUDA(cudaMemsetAsync(wk.Pnew, 0, (size_t)B * nn * 8, st));
+  SEQM_CUDA(cudaMemsetAsync(wk.Pold, 0, (size_t)B * nn * 8, st));
+  SEQM_CUDA(cudaMemsetAsync(F, 0, (size_t)B * nn * 8, st));
+  init_flags_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, nc, wk.err, niter, wk.EMAT);
+  SEQM_CHECK_LAUNCH("init_flags_kernel");
+  // F = fock(P), Eelec
+  rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, st);
+  if (rc) return rc;
+
+  unsigned long long* hstat = nullptr;
+  SEQM_CUDA(cudaMallocHost(&hstat, 64));
+  int k = 0;
+  long long left = B;
+  const int max_iter = opt->max_iter > 0 ? opt->max_iter : 1000;
+
+  auto density = [&](double* out) -> int {
+    if (opt->use_sp2)
+      return seqm_sp2_density(B, S, mmax, F, nheavy, nhydro, nocc, opt->sp2_eps, nc, out, nullptr, wk.sp2, st);
+    return launch_eigh_density(B, S, mmax, F, nheavy, nhydro, nocc, nc, out, nullptr, nullptr, nullptr, st);
+  };
+  auto refock_and_finish = [&](bool store, int& counter, int& cF) -> int {
+    int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, st);
+    if (r) return r;
+    if (store) {
+      cF = cF < NFOCK ? cF + 1 : NFOCK;
+      counter = (counter + 1) % NFOCK;
+      r = launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st);
+      if (r) return r;
+      pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
+      SEQM_CHECK_LAUNCH("pulay_store_kernel");
+      pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
+      SEQM_CHECK_LAUNCH("pulay_emat_kernel");
+    }
+    SEQM_CUDA(cudaMemsetAsync(wk.stat, 0, 16, st));
+    finish_step_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, opt->eps, wk.Enew, Eelec, wk.err, nc, niter, wk.stat);
+    SEQM_CHECK_LAUNCH("finish_step_kernel");
+    SEQM_CUDA(cudaMemcpyAsync(hstat, wk.stat, 16, cudaMemcpyDeviceToHost, st));
+    SEQM_CUDA(cudaStreamSynchronize(st));
+    left = (long long)hstat[0];
+    if (opt->debug) {
+      double mx;
+      long long bits = (long long)hstat[1];
+      memcpy(&mx, &bits, 8);
+      printf("scf  %d %.17g %lld\n", k, mx, left);
+      fflush(stdout);
+    }
+    ++k;
+    return SEQM_OK;
+  };
+  auto mix = [&](int mode) -> int {
+    mix_kernel<<<B, 256, 0, st>>>(n4, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold);
+    SEQM_CHECK_LAUNCH("mix_kernel");
+    return SEQM_OK;
+  };
+#define SEQM_TRY(x) do { rc = (x); if (rc) { cudaFreeHost(hstat); return rc; } } while (0)
+
+  int counter = -1, cF = 0;
+  if (opt->converger == 0) {
+    while (left > 0) {
+      SEQM_TRY(density(wk.Pnew));
+      SEQM_TRY(mix(MIX_CONST));
+      SEQM_TRY(refock_and_finish(false, counter, cF));
+      if (k >= max_iter) break;
+    }
+  } else {
+    bool done = false;
+    for (int i = 0; i < 2 && !done; ++i) {
+      if (left == 0) { done = true; break; }
+      SEQM_TRY(density(wk.Pnew));
+      SEQM_TRY(mix(MIX_DIRECT));
+      SEQM_TRY(refock_and_finish(false, counter, cF));
+    }
+    if (!done && opt->converger == 1) {
+      while (left > 0) {
+        SEQM_TRY(density(wk.Pnew));
+        SEQM_TRY(mix(MIX_ADAPTIVE));
+        SEQM_TRY(refock_and_finish(false, counter, cF));
+        if (k >= max_iter) break;
+      }
+    } else if (!done) {
+      if (left > 0) {
+        SEQM_TRY(density(wk.Pnew));
+        SEQM_TRY(mix(MIX_ADAPTIVE));
+        SEQM_TRY(refock_and_finish(false, counter, cF));
+      }
+      // two stores with direct steps (scf_loop.py:408-453): store uses the current F, P
+      while (cF < 2 && left > 0) {
+        cF = cF < NFOCK ? cF + 1 : NFOCK;
+        counter = (counter + 1) % NFOCK;
+        SEQM_TRY(launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st));
+        pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
+        pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
+        { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay store: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
+        SEQM_TRY(density(P));
+        SEQM_TRY(refock_and_finish(false, counter, cF));
+      }
+      while (left > 0) {
+        pulay_extrapolate_kernel<<<B, 256, 0, st>>>(n4, counter, cF, nc, wk.EMAT, wk.FOCK, F);
+        { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
+        SEQM_TRY(density(P));
+        SEQM_TRY(refock_and_finish(true, counter, cF));
+        if (k >= max_iter) break;
+      }
+    }
+  }
+  cudaFreeHost(hstat);
+  if (iterations_out) *iterations_out = k;
+  return SEQM_OK;
+}
+
+}  // extern "C"
