@@ -119,9 +119,9 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  * memory; supports packed size m <= seqm_eigh_max_m().
  *   nheavy,nhydro,nocc [B] int32;  e_out[B][n] (may be NULL) ascending orbital energies, zero padded;
  *   v_out[B][n][n] (may be NULL) eigenvectors in the reference's packed layout C[packed orbital][k];
- *   info[B] (may be NULL) sweeps used. */
+ *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
-int seqm_eigh_density(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy,
+int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                       double* e_out, double* v_out, int32_t* info, void* stream);
 
@@ -129,7 +129,7 @@ int seqm_eigh_density(int64_t nmol, int64_t molsize, const double* F, const int3
  * D[B][n][n] out (= 2 X, padded layout).  work: seqm_sp2_workspace(...) bytes of scratch.
  * niter[B] (may be NULL) multiplications used.  Synchronises the stream (host reads a counter). */
 size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize);
-int seqm_sp2_density(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy,
+int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
                      double* D, int32_t* niter, void* work, void* stream);
 
@@ -151,7 +151,7 @@ typedef struct {
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);
 int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss,
              const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
-             const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc,
+             const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, int mmax,
              const seqm_scf_options_t* opt, double* P, double* F, double* Eelec, uint8_t* notconverged,
              int32_t* niter, double* pairvec, void* work, int32_t* iterations_out, void* stream);
 
@@ -163,6 +163,11 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
 int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
                    int ngauss, const double* P, const double* D, const double* gE, const double* gNuc,
                    double* grad_xij, double* grad_rij, void* stream);
+
+/* C[b] = A[b] * B[b], square row-major fp64 matrices on the FP64 tensor pipe (building block of SP2 and of
+ * the Pulay commutator; exported for tests).  ld even, stride in elements, active[batch] may be NULL. */
+int seqm_dgemm_batched(int64_t n, int64_t ld, const double* A, const double* B, double* C, int64_t stride,
+                       int64_t batch, const uint8_t* active, void* stream);
 
 #ifdef __cplusplus
 }

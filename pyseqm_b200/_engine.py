@@ -1,0 +1,89 @@
+"""Host-side orchestration of one Hamiltonian build: topology (cached per pair list) -> per-atom records ->
+pair pass (hcore) -> device-resident SCF.  Used by seqm_functions.scf_loop.scf_loop, basics.Energy and
+XLBOMD.EnergyXL."""
+import time
+import warnings
+
+import torch
+
+from . import _ops
+from ._topology import PairTopology
+
+_TOPO_CACHE = []      # small LRU of (key tensors, PairTopology)
+_TOPO_CACHE_SIZE = 4
+
+
+def get_topology(nmol, molsize, Z, maskd, idxi, idxj, nHeavy, nHydro, nocc):
+    """PairTopology for these Parser tensors; reused while the pair list is unchanged (MD without cutoff
+    changes).  Validation compares the index tensors on the device (one sync)."""
+    for k, (cz, cm, ci, cj, co, topo) in enumerate(_TOPO_CACHE):
+        if (topo.nmol == nmol and topo.molsize == molsize and cz.shape == Z.shape and ci.shape == idxi.shape
+                and cz.device == Z.device):
+            same = torch.equal(ci, idxi) and torch.equal(cj, idxj) and torch.equal(cz, Z) and \
+                torch.equal(cm, maskd) and torch.equal(co, nocc)
+            if same:
+                if k:
+                    _TOPO_CACHE.insert(0, _TOPO_CACHE.pop(k))
+                return topo
+    topo = PairTopology(nmol, molsize, Z, maskd, idxi, idxj, nHeavy, nHydro, nocc)
+    _TOPO_CACHE.insert(0, (Z.clone(), maskd.clone(), idxi.clone(), idxj.clone(), nocc.clone(), topo))
+    del _TOPO_CACHE[_TOPO_CACHE_SIZE:]
+    return topo
+
+
+def initial_density(const, topo, Z, maskd):
+    """scf_loop.py:700-710: tore/4 on the four orbitals of a heavy atom, 1 on the hydrogen s orbital."""
+    B, S = topo.nmol, topo.molsize
+    Pb = torch.zeros(B * S * S, 4, 4, dtype=torch.float64, device=Z.device)
+    heavy = Z > 1
+    d = torch.zeros(Z.shape[0], 4, dtype=torch.float64, device=Z.device)
+    d[heavy] = (const.tore[Z[heavy]].to(torch.float64) / 4.0).unsqueeze(1)
+    d[Z == 1, 0] = 1.0
+    Pb[maskd] = torch.diag_embed(d)
+    return Pb.reshape(B, S, S, 4, 4).transpose(2, 3).reshape(B, 4 * S, 4 * S).contiguous()
+
+
+def _tic(const):
+    if const.do_timing:
+        torch.cuda.synchronize()
+        return time.time()
+    return None
+
+
+def _toc(const, key, t0):
+    if const.do_timing:
+        torch.cuda.synchronize()
+        const.timing.setdefault(key, []).append(time.time() - t0)
+
+
+def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters, method,
+          run_scf=True, P0=None, eps=1.0e-4, sp2=(False,), scf_converger=(1,), max_iter=1000, debug=False):
+    """-> state dict: topo, atompar, w, M, EnucAB, pv and (if run_scf) P, F, Eelec, notconverged, niter"""
+    for k in ('Kbeta', 'g_ss_nuc'):
+        if k in parameters:
+            raise NotImplementedError("parameter '%s' (learned-parameter feature) is outside the B200 hot path" % k)
+    topo = get_topology(int(nmol), int(molsize), Z, maskd, idxi, idxj, nHeavy, nHydro, nocc)
+    t0 = _tic(const)
+    with torch.no_grad():
+        atompar = _ops.atom_pack(topo, parameters, method)
+        w, M, EnucAB, pv = _ops.hcore(topo, atompar, xij, rij, parameters['U_ss'], parameters['U_pp'], method)
+    _toc(const, "Hcore + STO Integrals", t0)
+    st = dict(topo=topo, atompar=atompar, w=w, M=M, EnucAB=EnucAB, pv=pv, method=method)
+    par5 = tuple(parameters[k] for k in ('g_ss', 'g_pp', 'g_sp', 'g_p2', 'h_sp'))
+    st['par5'] = par5
+    if run_scf:
+        t0 = _tic(const)
+        with torch.no_grad():
+            P = initial_density(const, topo, Z, maskd) if not torch.is_tensor(P0) else P0
+            P, F, E, nc, nit, iters = _ops.scf(topo, w, M, par5, P, float(eps), list(scf_converger), list(sp2),
+                                               max_iter, debug, pv)
+        st.update(P=P, F=F, Eelec=E, notconverged=nc, niter=nit, iterations=iters)
+        if bool(nc.any()):
+            nnot = int(nc.sum())
+            warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (nnot, nmol, max_iter))
+        _toc(const, "SCF", t0)
+    return st
+
+
+def hcore_matrix(M, nmol, molsize):
+    return M.reshape(nmol, molsize, molsize, 4, 4).transpose(2, 3).reshape(nmol, 4 * molsize, 4 * molsize)

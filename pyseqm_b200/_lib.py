@@ -1,0 +1,85 @@
+"""ctypes binding of libseqm_b200.so (include/seqm_b200.h).  There is no fallback: if the library is
+missing or a call fails, an exception is raised."""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libseqm_b200.so')
+
+c_i32p = ctypes.POINTER(ctypes.c_int32)
+c_f64p = ctypes.POINTER(ctypes.c_double)
+c_u8p = ctypes.POINTER(ctypes.c_uint8)
+VP = ctypes.c_void_p
+
+
+class Topology(ctypes.Structure):
+    _fields_ = [('nmol', ctypes.c_int64), ('molsize', ctypes.c_int64), ('natoms', ctypes.c_int64),
+                ('npairs', ctypes.c_int64),
+                ('Z', VP), ('atom_mol', VP), ('atom_slot', VP), ('idxi', VP), ('idxj', VP), ('pair_cls', VP),
+                ('pair_slot', VP), ('cls_pairs', VP * 3), ('ncls', ctypes.c_int64 * 3),
+                ('start_i', VP), ('start_j', VP), ('perm_j', VP)]
+
+
+class WStore(ctypes.Structure):
+    _fields_ = [('wHH', VP), ('wXH', VP), ('wXX', VP)]
+
+
+class ScfOptions(ctypes.Structure):
+    _fields_ = [('converger', ctypes.c_int), ('alpha', ctypes.c_double), ('use_sp2', ctypes.c_int),
+                ('sp2_eps', ctypes.c_double), ('eps', ctypes.c_double), ('max_iter', ctypes.c_int),
+                ('debug', ctypes.c_int)]
+
+
+class SeqmError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises if it has not been built (python __graft_entry__.py / make -C csrc)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SeqmError("libseqm_b200.so not found at %s: build it with `make -C pyseqm_b200/csrc` "
+                            "(there is no CPU fallback)" % LIB_PATH)
+        L = ctypes.CDLL(LIB_PATH)
+        L.seqm_last_error.restype = ctypes.c_char_p
+        L.seqm_version.restype = ctypes.c_int
+        L.seqm_atompar_bytes.restype = ctypes.c_size_t
+        L.seqm_eigh_max_m.restype = ctypes.c_int
+        L.seqm_sp2_workspace.restype = ctypes.c_size_t
+        L.seqm_sp2_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64]
+        L.seqm_scf_workspace.restype = ctypes.c_size_t
+        L.seqm_scf_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ScfOptions)]
+        i64, ci, cd = ctypes.c_int64, ctypes.c_int, ctypes.c_double
+        TP = ctypes.POINTER(Topology)
+        L.seqm_atom_pack.argtypes = [i64] + [VP] * 13 + [ci, VP, VP]
+        L.seqm_hcore.argtypes = [TP, VP, VP, VP, VP, VP, ci, WStore, VP, VP, VP, VP]
+        L.seqm_w_expand.argtypes = [TP, WStore, VP, VP]
+        L.seqm_fock.argtypes = [TP, WStore] + [VP] * 12
+        L.seqm_elec_energy.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP]
+        L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
+        L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
+        L.seqm_scf.argtypes = [TP, WStore] + [VP] * 9 + [ci, ctypes.POINTER(ScfOptions)] + [VP] * 7 + \
+                              [ctypes.POINTER(ctypes.c_int32), VP]
+        L.seqm_pair_grad.argtypes = [TP, VP, VP, VP, ci] + [VP] * 7
+        L.seqm_dgemm_batched.argtypes = [i64, i64, VP, VP, VP, i64, i64, VP, VP]
+        for name in EXPORTS:
+            fn = getattr(L, name)
+            if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace'):
+                fn.restype = ctypes.c_int
+        _lib = L
+    return _lib
+
+
+EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
+           'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_density', 'seqm_sp2_workspace',
+           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched']
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().seqm_last_error()
+        raise SeqmError("%s failed (%d): %s" % (what, rc, msg.decode() if msg else ''))

@@ -1,0 +1,190 @@
+"""Thin op layer over the C ABI: allocates outputs with torch, passes raw device pointers and the
+current CUDA stream, and wraps the pair pass + its hand-written adjoint as a torch.autograd.Function so
+`Force`'s `L.backward()` and `ForceXL`'s `grad(L, coordinates)` work as in the reference."""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ScfOptions, WStore, check, lib
+from ._topology import PairTopology
+
+N_GAUSS = {'MNDO': 0, 'AM1': 4, 'PM3': 2}
+LAUNCHES = [0]      # C-ABI calls issued (bench.py reports kernel launches from its own counters)
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _f64(t):
+    if t.dtype != torch.float64:
+        raise TypeError("pyseqm_b200 computes in float64 only (got %s); call torch.set_default_dtype(torch.float64)" % t.dtype)
+    if not t.is_cuda:
+        raise RuntimeError("pyseqm_b200 runs on CUDA tensors only (there is no CPU path)")
+    return t.detach().contiguous()
+
+
+class WTensors:
+    """class-tiled two-centre integrals"""
+
+    def __init__(self, topo):
+        n0, n1, n2 = topo.w_sizes()
+        dev = topo.device
+        self.hh = torch.empty(n0, dtype=torch.float64, device=dev)
+        self.xh = torch.empty(n1, dtype=torch.float64, device=dev)
+        self.xx = torch.empty(n2, dtype=torch.float64, device=dev)
+        self.c = WStore(self.hh.data_ptr(), self.xh.data_ptr(), self.xx.data_ptr())
+
+
+def atom_pack(topo, par, method):
+    """parameters dict (per-atom vectors, reference basics.py:148-154) -> packed per-atom records"""
+    ng = N_GAUSS[method]
+    A = topo.natoms
+    out = torch.empty(A * lib().seqm_atompar_bytes(), dtype=torch.uint8, device=topo.device)
+    g = [None, None, None]
+    if ng:
+        for q, c in enumerate('KLM'):
+            g[q] = torch.stack([_f64(par['Gaussian%d_%s' % (k + 1, c)]) for k in range(ng)], dim=1).contiguous()
+    v = [_f64(par[k]) for k in ('zeta_s', 'zeta_p', 'beta_s', 'beta_p', 'g_ss', 'g_pp', 'g_p2', 'h_sp', 'alpha')]
+    check(lib().seqm_atom_pack(A, _p(topo.Z), *[_p(x) for x in v], _p(g[0]), _p(g[1]), _p(g[2]), ng, _p(out),
+                               _stream()), 'seqm_atom_pack')
+    return out
+
+
+def hcore(topo, atompar, xij, rij, U_ss, U_pp, method, want_enuc=True):
+    """-> (WTensors, M[B*S*S,4,4], EnucAB[P] or None, pairvec scratch)"""
+    dev = topo.device
+    w = WTensors(topo)
+    M = torch.zeros(topo.nmol * topo.molsize * topo.molsize, 4, 4, dtype=torch.float64, device=dev)
+    en = torch.empty(topo.npairs, dtype=torch.float64, device=dev) if want_enuc else None
+    pv = torch.empty(max(topo.npairs, 1) * 20, dtype=torch.float64, device=dev)
+    xij, rij, U_ss, U_pp = _f64(xij), _f64(rij), _f64(U_ss), _f64(U_pp)
+    check(lib().seqm_hcore(topo.ref(), _p(atompar), _p(xij), _p(rij), _p(U_ss), _p(U_pp), N_GAUSS[method], w.c,
+                           _p(M), _p(en), _p(pv), _stream()), 'seqm_hcore')
+    return w, M, en, pv
+
+
+def w_expand(topo, w):
+    out = torch.empty(topo.npairs, 10, 10, dtype=torch.float64, device=topo.device)
+    check(lib().seqm_w_expand(topo.ref(), w.c, _p(out), _stream()), 'seqm_w_expand')
+    return out
+
+
+def fock(topo, w, P, M, par5, pv=None, F=None, active=None, want_energy=False):
+    """par5 = (g_ss, g_pp, g_sp, g_p2, h_sp) per-atom vectors.  -> F (and Eelec)"""
+    n4 = 4 * topo.molsize
+    if F is None:
+        F = torch.zeros(topo.nmol, n4, n4, dtype=torch.float64, device=topo.device)
+    if pv is None:
+        pv = torch.empty(max(topo.npairs, 1) * 20, dtype=torch.float64, device=topo.device)
+    E = torch.zeros(topo.nmol, dtype=torch.float64, device=topo.device) if want_energy else None
+    P, M = _f64(P), _f64(M)
+    g = [_f64(x) for x in par5]
+    check(lib().seqm_fock(topo.ref(), w.c, _p(P), _p(M), *[_p(x) for x in g], _p(active), _p(F), _p(E), _p(pv),
+                          _stream()), 'seqm_fock')
+    return (F, E) if want_energy else F
+
+
+def elec_energy(P, F, M, nmol, molsize, D=None):
+    E = torch.zeros(nmol, dtype=torch.float64, device=P.device)
+    P, F, M = _f64(P), _f64(F), _f64(M)
+    Dc = _f64(D) if D is not None else None
+    check(lib().seqm_elec_energy(nmol, molsize, _p(P), _p(F), _p(M), _p(Dc), 1 if D is not None else 0, _p(None),
+                                 _p(E), _stream()), 'seqm_elec_energy')
+    return E
+
+
+def eigh_density(F, nheavy, nhydro, nocc, molsize, mmax, want_eig=False, active=None):
+    """-> P (and e[B,n], v[B,n,n] with the packed eigenvectors in the top-left m x m corner)"""
+    F = _f64(F)
+    B, n4 = F.shape[0], F.shape[1]
+    P = torch.zeros_like(F)
+    e = torch.zeros(B, n4, dtype=torch.float64, device=F.device) if want_eig else None
+    v = torch.zeros_like(F) if want_eig else None
+    check(lib().seqm_eigh_density(B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc), _p(active), _p(P),
+                                  _p(e), _p(v), _p(None), _stream()), 'seqm_eigh_density')
+    return (P, e, v) if want_eig else P
+
+
+def sp2_density(F, nheavy, nhydro, nocc, molsize, mmax, eps, active=None, want_niter=False):
+    F = _f64(F)
+    B = F.shape[0]
+    D = torch.zeros_like(F)
+    work = torch.empty(lib().seqm_sp2_workspace(B, molsize), dtype=torch.uint8, device=F.device)
+    nit = torch.zeros(B, dtype=torch.int32, device=F.device) if want_niter else None
+    check(lib().seqm_sp2_density(B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc), float(eps),
+                                 _p(active), _p(D), _p(nit), _p(work), _stream()), 'seqm_sp2_density')
+    return (D, nit) if want_niter else D
+
+
+def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv):
+    """-> P, F, Eelec, notconverged(bool), niter[B], iterations"""
+    dev = topo.device
+    B, S = topo.nmol, topo.molsize
+    n4 = 4 * S
+    opt = ScfOptions()
+    opt.converger = int(converger[0])
+    opt.alpha = float(converger[1]) if (len(converger) > 1 and int(converger[0]) == 0) else 0.0
+    opt.use_sp2 = 1 if sp2[0] else 0
+    opt.sp2_eps = float(sp2[1]) if sp2[0] else 0.0
+    opt.eps = float(eps)
+    opt.max_iter = int(max_iter)
+    opt.debug = 1 if debug else 0
+    if opt.converger not in (0, 1, 2):
+        raise ValueError("scf_converger should be [0, alpha], [1] or [2]")
+    P = _f64(P0).clone()
+    F = torch.empty(B, n4, n4, dtype=torch.float64, device=dev)
+    E = torch.zeros(B, dtype=torch.float64, device=dev)
+    nc = torch.ones(B, dtype=torch.uint8, device=dev)
+    nit = torch.zeros(B, dtype=torch.int32, device=dev)
+    work = torch.empty(lib().seqm_scf_workspace(B, S, ctypes.byref(opt)), dtype=torch.uint8, device=dev)
+    iters = ctypes.c_int32(0)
+    g = [_f64(x) for x in par5]
+    check(lib().seqm_scf(topo.ref(), w.c, _p(_f64(M)), *[_p(x) for x in g], _p(topo.nheavy), _p(topo.nhydro),
+                         _p(topo.nocc), int(topo.mmax), ctypes.byref(opt), _p(P), _p(F), _p(E), _p(nc), _p(nit),
+                         _p(pv), _p(work), ctypes.byref(iters), _stream()), 'seqm_scf')
+    return P, F, E, nc.bool(), nit, iters.value
+
+
+def pair_grad(topo, atompar, xij, rij, method, P, D, gE, gNuc):
+    gx = torch.empty(topo.npairs, 3, dtype=torch.float64, device=topo.device)
+    gr = torch.empty(topo.npairs, dtype=torch.float64, device=topo.device)
+    xij, rij, P = _f64(xij), _f64(rij), _f64(P)
+    Dc = _f64(D) if D is not None else None
+    gE = _f64(gE) if gE is not None else None
+    gNuc = _f64(gNuc) if gNuc is not None else None
+    check(lib().seqm_pair_grad(topo.ref(), _p(atompar), _p(xij), _p(rij), N_GAUSS[method], _p(P), _p(Dc), _p(gE),
+                               _p(gNuc), _p(gx), _p(gr), _stream()), 'seqm_pair_grad')
+    return gx, gr
+
+
+class PairEnergy(torch.autograd.Function):
+    """(xij, rij) -> (Eelec[B], EnucAB[P]) at fixed density.  The values were computed by the forward
+    kernels; backward is the fused adjoint kernel (seqm_pair_grad), i.e. exactly the part of the graph the
+    reference's autograd replays with SCF0 treating P as a constant (scf_loop.py:661-668)."""
+
+    @staticmethod
+    def forward(ctx, xij, rij, state):
+        ctx.state = state
+        ctx.save_for_backward(xij, rij)
+        return state['Eelec'].clone(), state['EnucAB'].clone()
+
+    @staticmethod
+    def backward(ctx, gE, gNuc):
+        xij, rij = ctx.saved_tensors
+        s = ctx.state
+        gx, gr = pair_grad(s['topo'], s['atompar'], xij, rij, s['method'], s['P'], s.get('D'), gE, gNuc)
+        return gx, gr, None
+
+
+def dgemm_batched(A, B):
+    A, B = _f64(A), _f64(B)
+    nb, n = A.shape[0], A.shape[1]
+    C = torch.zeros_like(A)
+    check(lib().seqm_dgemm_batched(n, n, _p(A), _p(B), _p(C), n * n, nb, _p(None), _stream()), 'seqm_dgemm_batched')
+    return C

@@ -1,0 +1,204 @@
+"""Parser, Pack_Parameters, Hamiltonian, Energy, Force — the API of the reference's seqm/basics.py (same
+constructor dicts, call signatures and return tuples), with the numerical work done by the sm_100a kernels
+of libseqm_b200.so.  Tensors must be CUDA float64."""
+import os
+import time
+
+import torch
+
+from . import _engine, _ops
+from .seqm_functions import scf_loop as _scf_loop_mod
+from .seqm_functions.constants import ev
+from .seqm_functions.energy import elec_energy_isolated_atom, heat_formation, total_energy
+from .seqm_functions.parameters import params
+from .seqm_functions.scf_loop import scf_loop
+
+_BASE = ['U_ss', 'U_pp', 'zeta_s', 'zeta_p', 'beta_s', 'beta_p', 'g_ss', 'g_sp', 'g_pp', 'g_p2', 'h_sp', 'alpha']
+
+
+def _gauss(n):
+    return ['Gaussian%d_%s' % (k, c) for c in 'KLM' for k in range(1, n + 1)]
+
+
+parameterlist = {'AM1': _BASE + _gauss(4), 'MNDO': list(_BASE), 'PM3': _BASE + _gauss(2)}
+
+
+class Parser(torch.nn.Module):
+    """species/coordinates -> the 16 index and geometry tensors of reference basics.py:43-118.
+    Pairs are ordered (molecule, a, b) with a < b, exactly like the reference's boolean-mask selection;
+    the arithmetic on coordinates uses the same operations so xij and rij agree bit for bit."""
+
+    def __init__(self, seqm_parameters):
+        super().__init__()
+        self.outercutoff = seqm_parameters['pair_outer_cutoff']
+        self.elements = seqm_parameters['elements']
+
+    def forward(self, constansts, species, coordinates, *args, **kwargs):
+        device = coordinates.device
+        nmol, molsize = species.shape
+        nonblank = species > 0
+        flat = nonblank.reshape(-1)
+        real_atoms = torch.nonzero(flat).reshape(-1)
+        n_real = real_atoms.shape[0]
+        inv_real_atoms = torch.zeros((nmol * molsize,), device=device, dtype=torch.int64)
+        inv_real_atoms[real_atoms] = torch.arange(n_real, device=device, dtype=torch.int64)
+        Z = species.reshape(-1)[real_atoms]
+        nHeavy = torch.sum(species > 1, dim=1)
+        nHydro = torch.sum(species == 1, dim=1)
+        n_charge = torch.sum(constansts.tore[species], dim=1).reshape(-1).type(torch.int64)
+        if 'charges' in kwargs and torch.is_tensor(kwargs['charges']):
+            n_charge = n_charge - kwargs['charges'].reshape(-1).type(torch.int64)
+        nocc = torch.div(n_charge, 2, rounding_mode='floor')
+        if ((n_charge % 2) == 1).any():
+            raise ValueError("Only closed shell system (with even number of electrons) are supported")
+        mol_of = torch.arange(nmol, device=device, dtype=torch.int64).repeat_interleave(molsize)
+        slot_of = torch.arange(molsize, device=device, dtype=torch.int64).repeat(nmol)
+        maskd = (mol_of * molsize * molsize + slot_of * (molsize + 1))[real_atoms]
+        atom_molid = mol_of[real_atoms]
+        # all a < b slot pairs, row-major = (a, b) lexicographic
+        a, b = torch.triu_indices(molsize, molsize, offset=1, device=device)
+        npm = a.shape[0]
+        paircoord_raw = coordinates[:, b, :] - coordinates[:, a, :]            # R_b - R_a
+        pairdist2 = (paircoord_raw ** 2).sum(dim=2)
+        pairdist2 = torch.where(pairdist2 == 0.0, torch.full_like(pairdist2, 1.0e-4), pairdist2)
+        pairdist_raw = torch.sqrt(pairdist2)
+        keep = (nonblank[:, a] & nonblank[:, b] & (pairdist_raw < self.outercutoff)).reshape(-1)
+        paircoord = paircoord_raw.reshape(-1, 3)[keep]
+        pairdist = pairdist_raw.reshape(-1)[keep]
+        rij = pairdist * constansts.length_conversion_factor
+        molp = torch.arange(nmol, device=device, dtype=torch.int64).unsqueeze(1).expand(nmol, npm).reshape(-1)[keep]
+        first = molp * molsize + a.repeat(nmol)[keep]
+        second = molp * molsize + b.repeat(nmol)[keep]
+        idxi = inv_real_atoms[first]
+        idxj = inv_real_atoms[second]
+        ni = Z[idxi]
+        nj = Z[idxj]
+        xij = paircoord / pairdist.unsqueeze(1)
+        mask = first * molsize + second % molsize
+        pair_molid = molp
+        return nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij
+
+
+class Pack_Parameters(torch.nn.Module):
+    """per-atom parameter vectors p[Z, i] (reference basics.py:120-154)"""
+
+    def __init__(self, seqm_parameters):
+        super().__init__()
+        self.elements = seqm_parameters['elements']
+        self.learned_list = seqm_parameters['learned']
+        self.method = seqm_parameters['method']
+        self.filedir = seqm_parameters['parameter_file_dir'] if 'parameter_file_dir' in seqm_parameters \
+            else os.path.abspath(os.path.dirname(__file__)) + '/params/'
+        self.parameters = parameterlist[self.method]
+        self.required_list = [name for name in self.parameters if name not in self.learned_list]
+        self.nrp = len(self.required_list)
+        self.p = params(method=self.method, elements=self.elements, root_dir=self.filedir,
+                        parameters=self.required_list)
+
+    def forward(self, Z, learned_params=dict()):
+        for i in range(self.nrp):
+            learned_params[self.required_list[i]] = self.p[Z, i]
+        return learned_params
+
+
+class Hamiltonian(torch.nn.Module):
+    """SCF (reference basics.py:156-251): -> F, e, P, Hcore, w, charge, notconverged"""
+
+    def __init__(self, seqm_parameters):
+        super().__init__()
+        self.eps = torch.nn.Parameter(torch.as_tensor(seqm_parameters['scf_eps']), requires_grad=False)
+        self.sp2 = seqm_parameters['sp2']
+        self.scf_converger = seqm_parameters['scf_converger']
+        self.eig = seqm_parameters.get('eig', False)
+        self.scf_backward = seqm_parameters.get('scf_backward', 0)
+        if 'scf_backward_eps' not in seqm_parameters:
+            seqm_parameters['scf_backward_eps'] = 1.0e-2
+        self.scf_backward_eps = torch.nn.Parameter(torch.as_tensor(seqm_parameters['scf_backward_eps']),
+                                                   requires_grad=False)
+        if self.scf_backward != 0:
+            raise NotImplementedError("scf_backward=1/2 is outside the B200 hot path (see DESIGN.md)")
+
+    def forward(self, const, molsize, nHeavy, nHydro, nocc, Z, maskd, mask, atom_molid, pair_molid, idxi, idxj, ni,
+                nj, xij, rij, parameters, P0=None):
+        beta = torch.cat((parameters['beta_s'].unsqueeze(1), parameters['beta_p'].unsqueeze(1)), dim=1)
+        Kbeta = parameters["Kbeta"] if "Kbeta" in parameters else None
+        return scf_loop(const=const, molsize=molsize, nHeavy=nHeavy, nHydro=nHydro, nOccMO=nocc, maskd=maskd,
+                        mask=mask, atom_molid=atom_molid, pair_molid=pair_molid, idxi=idxi, idxj=idxj, ni=ni, nj=nj,
+                        xij=xij, rij=rij, Z=Z, zetas=parameters['zeta_s'], zetap=parameters['zeta_p'],
+                        uss=parameters['U_ss'], upp=parameters['U_pp'], gss=parameters['g_ss'],
+                        gsp=parameters['g_sp'], gpp=parameters['g_pp'], gp2=parameters['g_p2'],
+                        hsp=parameters['h_sp'], beta=beta, Kbeta=Kbeta, eps=self.eps, P=P0, sp2=self.sp2,
+                        scf_converger=self.scf_converger, eig=self.eig, scf_backward=self.scf_backward,
+                        scf_backward_eps=self.scf_backward_eps)
+
+
+class Energy(torch.nn.Module):
+    """Energies (reference basics.py:253-346).  Parser -> parameters -> pair pass + SCF kernels; Eelec and
+    EnucAB come out of one autograd node whose backward is the fused adjoint kernel."""
+
+    def __init__(self, seqm_parameters):
+        super().__init__()
+        self.seqm_parameters = seqm_parameters
+        self.method = seqm_parameters['method']
+        self.parser = Parser(seqm_parameters)
+        self.packpar = Pack_Parameters(seqm_parameters)
+        self.hamiltonian = Hamiltonian(seqm_parameters)
+        self.Hf_flag = seqm_parameters.get("Hf_flag", True)
+
+    def forward(self, const, coordinates, species, learned_parameters=dict(), all_terms=False, P0=None, step=0,
+                *args, **kwargs):
+        nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
+            self.parser(const, species, coordinates, *args, **kwargs)
+        if callable(learned_parameters):
+            parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
+        else:
+            parameters = self.packpar(Z, learned_params=learned_parameters)
+        for k, v in parameters.items():
+            if torch.is_tensor(v) and v.requires_grad:
+                raise NotImplementedError("gradients with respect to parameter '%s' are outside the B200 hot path" % k)
+        H = self.hamiltonian
+        st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
+                           self.method, run_scf=True, P0=P0, eps=float(H.eps), sp2=H.sp2,
+                           scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER, debug=_scf_loop_mod.debug)
+        P, notconverged = st['P'], st['notconverged']
+        Eelec, EnucAB = _ops.PairEnergy.apply(xij, rij, st)
+        e = charge = None
+        if H.eig:
+            from .seqm_functions.diag import sym_eig_trunc
+            from .seqm_functions.scf_loop import _charges
+            e, v = sym_eig_trunc(st['F'], nHeavy, nHydro, nocc, eig_only=True)
+            charge = _charges(v, nHeavy, nHydro, nmol, molsize)
+        self.last_state = st
+        if all_terms:
+            Etot, Enuc = total_energy(nmol, pair_molid, EnucAB, Eelec)
+            Eiso = elec_energy_isolated_atom(const, Z, uss=parameters['U_ss'], upp=parameters['U_pp'],
+                                             gss=parameters['g_ss'], gpp=parameters['g_pp'], gsp=parameters['g_sp'],
+                                             gp2=parameters['g_p2'], hsp=parameters['h_sp'])
+            Hf, Eiso_sum = heat_formation(const, nmol, atom_molid, Z, Etot, Eiso, flag=self.Hf_flag)
+            return Hf, Etot, Eelec, Enuc, Eiso_sum, EnucAB, e, P, charge, notconverged
+        return Eelec, EnucAB, P, notconverged
+
+
+class Force(torch.nn.Module):
+    """force = -dHf/dR (reference basics.py:348-390)"""
+
+    def __init__(self, seqm_parameters):
+        super().__init__()
+        self.energy = Energy(seqm_parameters)
+        self.create_graph = seqm_parameters.get("2nd_grad", False)
+        if self.create_graph:
+            raise NotImplementedError("2nd_grad (second derivatives) is outside the B200 hot path")
+        self.seqm_parameters = seqm_parameters
+
+    def forward(self, const, coordinates, species, learned_parameters=dict(), P0=None, step=0, *args, **kwargs):
+        coordinates.requires_grad_(True)
+        Hf, Etot, Eelec, Enuc, Eiso, EnucAB, e, P, charge, notconverged = \
+            self.energy(const, coordinates, species, learned_parameters=learned_parameters, all_terms=True, P0=P0,
+                        step=step, *args, **kwargs)
+        L = Hf.sum()
+        t0 = _engine._tic(const)
+        L.backward()
+        _engine._toc(const, "Force", t0)
+        force = -coordinates.grad.detach()
+        coordinates.grad = torch.zeros_like(coordinates.grad)
+        return force, P, Etot, Hf, Eelec, Enuc, Eiso, EnucAB, e, charge, notconverged

@@ -6,6 +6,7 @@
 // the analogue of the reference's notconverged.any().
 // reference: seqm/seqm_functions/scf_loop.py:32-510 (iteration schedule and EMAT/EVEC ring arithmetic,
 // including the stale-lower-triangle quirk after the ring wraps, scf_loop.py:460-490)
+#include <cstring>
 #include <vector>
 
 #include "abi_common.cuh"

@@ -1,0 +1,141 @@
+"""Parity of the CUDA path (called through the C ABI / the seqm.basics-style API) against the golden
+vectors of the unmodified reference and against the oracle.  Tolerances (BASELINE.json north_star):
+Parser tensors bit-exact; w, M, EnucAB 1e-11 (direct formulas); F, P 1e-9 given the same inputs;
+Etot/Eelec 1e-6 eV; forces 1e-5 eV/A; SCF iteration sequence identical."""
+import contextlib
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN, golden_names
+
+pytestmark = pytest.mark.gpu
+torch.set_default_dtype(torch.float64)
+ELEMENTS = [0, 1, 6, 7, 8]
+# N2: DIIS error vectors vanish by symmetry -> Pulay coefficients are rounding noise (see test_oracle_golden)
+NOISE_DIIS = {'small_PM3_eigh_c2': [1], 'small_MNDO_eigh_c2': [1]}
+
+
+def _dev():
+    assert torch.cuda.is_available()
+    return torch.device('cuda:0')
+
+
+def _load(name):
+    return np.load(os.path.join(GOLDEN, name + '.npz'))
+
+
+def _params(g):
+    sp2 = g['sp2'].tolist()
+    conv = g['conv'].tolist()
+    conv[0] = int(conv[0])
+    return dict(method=str(g['method']), scf_eps=float(g['eps']), scf_converger=conv,
+                sp2=[bool(sp2[0])] + sp2[1:], elements=ELEMENTS, learned=[], pair_outer_cutoff=1.0e10)
+
+
+def _t(x, dev):
+    return torch.as_tensor(np.asarray(x)).to(dev)
+
+
+def test_dgemm_matches_matmul():
+    from pyseqm_b200 import _ops
+    dev = _dev()
+    g = torch.Generator(device='cpu').manual_seed(0)
+    for n, nb in ((48, 7), (120, 3), (240, 2), (64, 1), (250, 2)):
+        A = torch.randn(nb, n, n, generator=g).to(dev)
+        B = torch.randn(nb, n, n, generator=g).to(dev)
+        C = _ops.dgemm_batched(A, B)
+        ref = torch.matmul(A, B)
+        assert float((C - ref).abs().max()) < 1e-11 * n, n
+
+
+@pytest.mark.parametrize('name', golden_names())
+def test_hcore_fock_density_ops(name):
+    """op-level parity on the reference's own intermediate tensors"""
+    from pyseqm_b200 import _engine, _ops
+    from pyseqm_b200.basics import Pack_Parameters, Parser
+    from pyseqm_b200.seqm_functions.constants import Constants
+    dev = _dev()
+    g = _load(name)
+    sp = _params(g)
+    const = Constants().to(dev)
+    species, coords = _t(g['species'], dev), _t(g['coords'], dev)
+    nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
+        Parser(sp)(const, species, coords)
+    for k, v in (('maskd', maskd), ('mask', mask), ('idxi', idxi), ('idxj', idxj), ('xij', xij), ('rij', rij)):
+        assert np.array_equal(v.cpu().numpy(), g[k]), k
+    par = Pack_Parameters(sp).to(dev)(Z, learned_params=dict())
+    st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, par, sp['method'],
+                       run_scf=False)
+    topo = st['topo']
+    assert float((st['M'].cpu() - torch.as_tensor(g['M'])).abs().max()) < 1e-11
+    assert float((st['EnucAB'].cpu() - torch.as_tensor(g['EnucAB'])).abs().max()) < 1e-11
+    w = _ops.w_expand(topo, st['w']).cpu()
+    if 'w' in g:
+        assert float((w - torch.as_tensor(g['w'])).abs().max()) < 1e-12
+    else:
+        assert float((w.sum(dim=(1, 2)) - torch.as_tensor(g['w_sum'])).abs().max()) < 1e-11
+        assert float((w[:, 0, 0] - torch.as_tensor(g['w_00'])).abs().max()) < 1e-12
+    # fock at the reference's converged density
+    Pg = _t(g['P'], dev)
+    F, E = _ops.fock(topo, st['w'], Pg, st['M'], st['par5'], want_energy=True)
+    assert float((F.cpu() - torch.as_tensor(g['F'])).abs().max()) < 1e-10
+    assert float((E.cpu() - torch.as_tensor(g['Eelec'])).abs().max()) < 1e-9
+    # density from the reference's Fock matrix, both solvers
+    import seqm_oracle as orc
+    Fg = torch.as_tensor(g['F'])
+    Pref = orc.density_eigh(Fg, torch.as_tensor(g['nHeavy']), torch.as_tensor(g['nHydro']), torch.as_tensor(g['nocc']))
+    if topo.mmax <= 118:
+        Pn, e, v = _ops.eigh_density(_t(g['F'], dev), topo.nheavy, topo.nhydro, topo.nocc, molsize, topo.mmax,
+                                     want_eig=True)
+        keep = np.ones(nmol, dtype=bool)
+        keep[NOISE_DIIS.get(name, [])] = False
+        assert float((Pn.cpu() - Pref).abs()[keep].max()) < 1e-9
+        _, eref, _ = orc.density_eigh(Fg, torch.as_tensor(g['nHeavy']), torch.as_tensor(g['nHydro']),
+                                      torch.as_tensor(g['nocc']), want_eig=True)
+        assert float((e.cpu() - eref).abs().max()) < 1e-10
+    same_size = len(set((4 * g['nHeavy'] + g['nHydro']).tolist())) == 1
+    if same_size:
+        D = _ops.sp2_density(_t(g['F'], dev), topo.nheavy, topo.nhydro, topo.nocc, molsize, topo.mmax, 1e-7)
+        Dref, _ = orc.sp2_density(orc.pack(Fg, torch.as_tensor(g['nHeavy']), torch.as_tensor(g['nHydro'])),
+                                  torch.as_tensor(g['nocc']), 1e-7)
+        Dref = orc.unpack(Dref, torch.as_tensor(g['nHeavy']), torch.as_tensor(g['nHydro']), 4 * molsize)
+        assert float((D.cpu() - Dref).abs().max()) < 1e-9
+
+
+def _mixed_sizes(g):
+    return len(set((4 * g['nHeavy'] + g['nHydro']).tolist())) > 1
+
+
+@pytest.mark.parametrize('name', golden_names())
+def test_force_end_to_end(name):
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.seqm_functions.constants import Constants
+    from pyseqm_b200.seqm_functions import scf_loop
+    dev = _dev()
+    g = _load(name)
+    sp = _params(g)
+    if sp['sp2'][0] and _mixed_sizes(g):
+        pytest.skip("SP2 on mixed-size batches: the reference's zero-padding quirk is not reproduced (DESIGN.md)")
+    const = Constants().to(dev)
+    species, coords = _t(g['species'], dev), _t(g['coords'], dev)
+    scf_loop.debug = True
+    try:
+        force, P, Etot, Hf, Eelec, Enuc, Eiso, EnucAB, e, charge, notconv = Force(sp).to(dev)(const, coords, species)
+    finally:
+        scf_loop.debug = False
+    torch.cuda.synchronize()
+    keep = np.ones(g['species'].shape[0], dtype=bool)
+    keep[NOISE_DIIS.get(name, [])] = False
+    d = lambda a, k: float((a.detach().cpu() - torch.as_tensor(g[k])).abs()[keep].max())
+    assert d(Etot, 'Etot') < 1e-6
+    assert d(Eelec, 'Eelec') < 1e-6
+    assert d(Hf, 'Hf') < 1e-6
+    assert d(Enuc, 'Enuc') < 1e-9
+    assert d(Eiso, 'Eiso') < 1e-9
+    assert np.array_equal(notconv.cpu().numpy(), g['notconverged'])
+    assert d(P, 'P') < 1e-7, d(P, 'P')
+    assert d(force, 'force') < 1e-5, d(force, 'force')
