@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""Benchmark of the batched SCF hot path (BASELINE.json config 2): AM1 SCF + forces for a batch of 1024
+perturbed benzene geometries (12 atoms, 30 orbitals), eigh density path; metric = SCF molecules / second.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl]
+
+One step = one `Force` call (Parser + pair pass + SCF + force adjoint) over the whole batch.  `value` is
+timed with the coordinates resident in HBM; `e2e` includes, every step, the host->device copy of the
+coordinates from pinned memory and the device->host copy of forces and energies.  N > 1: one process per
+GPU (torchrun), every rank runs its own 1024-molecule shard (weak scaling), no collective in the loop,
+one all_gather of the energies at the end of every step.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+torch.set_default_dtype(torch.float64)
+
+NMOL = 1024
+SEQM_PAR = dict(method='AM1', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6], learned=[],
+                pair_outer_cutoff=1.0e10)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+            'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                t = [x.strip() for x in out.strip().split(',')]
+                if len(t) >= 6:
+                    self.rows.append(t)
+            except Exception:
+                pass
+            time.sleep(0.15)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def run_reference(args, rank, world):
+    """The reference's algorithm on the host cores (oracle port: the reference itself is a Python package that
+    does not exist on the GPU box).  Each step = a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import seqm_oracle as orc
+    from pyseqm_b200 import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    nsample = 128
+    sp, xyz = synth.benzene(nsample, seed=0)
+    species, coords = torch.as_tensor(sp), torch.as_tensor(xyz)
+    times = []
+    for it in range(args.warmup + args.steps):
+        t0 = time.time()
+        orc.run(species, coords, method='AM1', scf_eps=1e-6, converger=(2, 0.0))
+        if it >= args.warmup:
+            times.append(time.time() - t0)
+    ms = 1e3 * sum(times) / len(times)
+    val = nsample / (ms * 1e-3)
+    sample = "%d of the 1024 perturbed benzenes per step (same generator, seed 0)" % nsample
+    print(json.dumps({
+        "impl": "reference", "metric": "SCF molecules/sec", "value": val, "unit": "molecules/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "AM1 SCF+forces, perturbed benzene (12 atoms, 30 orbitals), eigh, converger [2], "
+                               "scf_eps 1e-6", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "molecules/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def algorithmic_bytes(topo):
+    """bytes one launch group must move at least once, per kernel"""
+    nHH, nXH, nXX = topo.ncls
+    A, B, S, m = topo.natoms, topo.nmol, topo.molsize, topo.mmax
+    blk = {0: 8, 1: 32, 2: 128}              # bytes of one P/M/F block of the class (1, 4, 16 doubles)
+    wb = {0: 8, 1: 80, 2: 800}               # integrals of one pair
+    pv = {0: 16, 1: 88, 2: 160}              # Coulomb vectors written per pair
+    n = {0: nHH, 1: nXH, 2: nXX}
+    fock_pair = sum(n[c] * (wb[c] + 2 * blk[c] + 2 * blk[c] + pv[c] + 16) for c in range(3))
+    fock_diag = A * (80 + 80 + 2 * 80) + sum(n[c] * pv[c] for c in range(3))
+    pair_fwd = sum(n[c] * (32 + 16 + wb[c] + 128 + 8 + pv[c]) for c in range(3)) + A * 224
+    pair_grad = sum(n[c] * (32 + 16 + 3 * blk[c] + 32) for c in range(3)) + A * 224
+    eigh = B * 2 * m * m * 8
+    return dict(fock_pair=fock_pair, fock_diag=fock_diag, fock=fock_pair + fock_diag, pair_fwd=pair_fwd,
+                pair_grad=pair_grad, eigh_density=eigh)
+
+
+def time_op(fn, flush, reps=5):
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    fn()
+    for a, b in ev:
+        flush()
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in ev) / reps
+
+
+def run_gpu(args, rank, world, local_rank):
+    import ctypes
+    from pyseqm_b200 import _lib, _ops, synth
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.seqm_functions.constants import Constants
+    dev = torch.device('cuda', local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
+    L = _lib.lib()
+    sp, xyz = synth.benzene(NMOL, seed=rank)
+    species = torch.as_tensor(sp).to(dev)
+    coords_host = torch.as_tensor(xyz).pin_memory()
+    coords = coords_host.to(dev)
+    const = Constants().to(dev)
+    force_mod = Force(dict(SEQM_PAR)).to(dev)
+    flush_buf = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)     # > 126 MB of L2
+
+    def flush():
+        flush_buf.fill_(1)
+
+    gathered = [torch.empty(NMOL, device=dev) for _ in range(world)] if world > 1 else None
+
+    def step(x):
+        out = force_mod(const, x, species)
+        if world > 1:
+            dist.all_gather(gathered, out[2].detach())
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        out = step(coords.clone())
+    nconv_fail = int(out[10].sum())
+    # ---- resident-input timing ----
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = L.seqm_launch_count()
+    evs = []
+    for _ in range(args.steps):
+        x = coords.clone()
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step(x)
+        b.record()
+        evs.append((a, b))
+    barrier()
+    launches = int(L.seqm_launch_count() - l0)
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    # ---- end to end: pinned host coordinates in, forces + energies out, every step ----
+    f_host = torch.empty(NMOL, 12, 3).pin_memory()
+    e_host = torch.empty(NMOL).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        x = coords_host.to(dev, non_blocking=True)
+        o = step(x)
+        f_host.copy_(o[0], non_blocking=True)
+        e_host.copy_(o[2].detach(), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    sampler.stop_flag = True
+    t = torch.tensor([total_ms, e2e_ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- per-kernel profile of one step, and the kernels timed alone on the converged state ----
+    L.seqm_profile_enable(1)
+    step(coords.clone())
+    buf = ctypes.create_string_buffer(1 << 16)
+    L.seqm_profile_report(buf, len(buf))
+    L.seqm_profile_enable(0)
+    prof = {}
+    for line in buf.value.decode().splitlines():
+        nm, ms, cnt = line.rsplit(' ', 2)
+        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
+    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
+    for v in prof.values():
+        v["share"] = v["ms"] / tot_prof
+    st = force_mod.energy.last_state
+    topo = st['topo']
+    ab = algorithmic_bytes(topo)
+    hbm, peak_src = peaks()
+    xij = torch.randn(topo.npairs, 3, device=dev)
+    xij = xij / xij.norm(dim=1, keepdim=True)
+    rij = torch.rand(topo.npairs, device=dev) * 6 + 2
+    par = force_mod.energy.packpar(topo.Z.long(), learned_params=dict())
+    ops = {
+        'fock': lambda: _ops.fock(topo, st['w'], st['P'], st['M'], st['par5'], pv=st['pv'], F=st['F']),
+        'eigh_density': lambda: _ops.eigh_density(st['F'], topo.nheavy, topo.nhydro, topo.nocc, topo.molsize, topo.mmax),
+        'pair_fwd': lambda: _ops.hcore(topo, st['atompar'], xij, rij, par['U_ss'], par['U_pp'], 'AM1'),
+        'pair_grad': lambda: _ops.pair_grad(topo, st['atompar'], xij, rij, 'AM1', st['P'], None, None, None),
+    }
+    kernels = {}
+    for nm, fn in ops.items():
+        ms = time_op(fn, flush)
+        kernels[nm] = {"ms_per_launch": ms, "algorithmic_bytes": ab[nm], "achieved_gbs": ab[nm] / (ms * 1e-3) / 1e9,
+                       "frac_of_hbm": ab[nm] / (ms * 1e-3) / 1e9 / hbm}
+    group = {'fock': ('fock_pair', 'fock_diag'), 'eigh_density': ('eigh_density',), 'pair_fwd': ('pair_fwd',),
+             'pair_grad': ('pair_grad',)}
+    share = {k: sum(prof.get(g, {"share": 0.0})["share"] for g in gs) for k, gs in group.items()}
+    top = max(share, key=share.get)
+    roof = {"bound": "hbm", "kernel": top, "share_of_step": share[top], "achieved": kernels[top]["achieved_gbs"],
+            "peak": hbm, "peak_source": peak_src, "unit": "GB/s", "frac": kernels[top]["frac_of_hbm"], "traffic": None}
+    # ---- CPU baseline: the oracle port on a bounded sample, all host cores ----
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import seqm_oracle as orc
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ns = 128
+    t0 = time.time()
+    orc.run(torch.as_tensor(sp[:ns]), torch.as_tensor(xyz[:ns]), method='AM1', scf_eps=1e-6, converger=(2, 0.0))
+    cpu_s = time.time() - t0
+    ms_step = total_ms / args.steps
+    nm_total = NMOL * world
+    print(json.dumps({
+        "metric": "SCF molecules/sec", "value": nm_total / (ms_step * 1e-3), "unit": "molecules/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "AM1 SCF+forces, 1024 perturbed benzenes per GPU (12 atoms, 30 orbitals), eigh, "
+                               "converger [2], scf_eps 1e-6 (BASELINE.json configs[1])",
+                   "molecules_per_gpu": NMOL, "l2": "192 MiB buffer written between timed steps",
+                   "scf_not_converged": nconv_fail, "scf_iterations": int(st['iterations'])},
+        "e2e": {"value": nm_total / (e2e_ms / args.steps * 1e-3), "unit": "molecules/s",
+                "h2d_bytes_per_step": NMOL * 12 * 3 * 8, "d2h_bytes_per_step": NMOL * 12 * 3 * 8 + NMOL * 8},
+        "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
+        "profile_one_step": prof,
+        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": "port",
+                         "sample": "first %d of the 1024 benzenes, one Force-equivalent call of the oracle" % ns}}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+    else:
+        run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

@@ -72,6 +72,12 @@ typedef struct {
 } seqm_w_t;
 
 const char* seqm_last_error(void);
+/* kernels launched by this library since load (bench.py's gpu_launches) */
+unsigned long long seqm_launch_count(void);
+/* optional CUDA-event profiler: regions between consecutive launches groups; report() synchronises and writes
+ * "name total_ms count" lines */
+void seqm_profile_enable(int on);
+int seqm_profile_report(char* buf, size_t cap);
 int seqm_version(void);
 size_t seqm_atompar_bytes(void); /* size of one packed per-atom record (seqm_atom_pack output) */
 

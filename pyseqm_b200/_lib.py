@@ -47,6 +47,10 @@ def lib():
         L = ctypes.CDLL(LIB_PATH)
         L.seqm_last_error.restype = ctypes.c_char_p
         L.seqm_version.restype = ctypes.c_int
+        L.seqm_launch_count.restype = ctypes.c_ulonglong
+        L.seqm_profile_enable.argtypes = [ctypes.c_int]
+        L.seqm_profile_enable.restype = None
+        L.seqm_profile_report.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
         L.seqm_atompar_bytes.restype = ctypes.c_size_t
         L.seqm_eigh_max_m.restype = ctypes.c_int
         L.seqm_sp2_workspace.restype = ctypes.c_size_t
@@ -68,13 +72,14 @@ def lib():
         L.seqm_dgemm_batched.argtypes = [i64, i64, VP, VP, VP, i64, i64, VP, VP]
         for name in EXPORTS:
             fn = getattr(L, name)
-            if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace'):
+            if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
+                            'seqm_launch_count', 'seqm_profile_enable'):
                 fn.restype = ctypes.c_int
         _lib = L
     return _lib
 
 
-EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
+EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_density', 'seqm_sp2_workspace',
            'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched']
 

@@ -10,6 +10,10 @@
 namespace seqm {
 
 void set_error(const std::string& s);
+// launch accounting and the optional event profiler (seqm_profile_*): prof_mark(name) opens a region that
+// lasts until the next mark on the same stream
+extern unsigned long long g_launches;
+void prof_mark(const char* name, cudaStream_t st);
 
 inline int fail(int code, const char* what) {
   set_error(what);
@@ -21,6 +25,7 @@ inline int fail(int code, const char* what) {
 
 #define SEQM_CHECK_LAUNCH(name)                                                            \
   do {                                                                                     \
+    ++::seqm::g_launches;                                                                  \
     cudaError_t e_ = cudaGetLastError();                                                   \
     if (e_ != cudaSuccess) {                                                               \
       ::seqm::set_error(std::string(name) + ": " + cudaGetErrorString(e_));                \

@@ -132,8 +132,10 @@ int launch_dgemm_batched(int n, int ld, const double* A, const double* B, double
     return SEQM_OK;
   }
   dim3 grid(cdiv(n, BN), cdiv(n, BM), batch);
+  prof_mark("dgemm", st);
   dgemm_batched_kernel<<<grid, 256, 0, st>>>(n, ld, A, B, C, stride, active, dims);
   SEQM_CHECK_LAUNCH("dgemm_batched_kernel");
+  prof_mark("end", st);
   return SEQM_OK;
 }
 

@@ -190,9 +190,11 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
     SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
+  prof_mark("eigh_density", st);
   eigh_density_kernel<<<(unsigned)nmol, threads, smem, st>>>((int)molsize, mp, F, nheavy, nhydro, nocc, active, P,
                                                            e_out, v_out, info);
   SEQM_CHECK_LAUNCH("eigh_density_kernel");
+  prof_mark("end", st);
   return SEQM_OK;
 }
 

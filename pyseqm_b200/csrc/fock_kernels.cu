@@ -194,6 +194,7 @@ elec_energy_kernel(int S, const double* __restrict__ P, const double* __restrict
 int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const double* M, const double* g_ss,
                 const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
                 const uint8_t* active, double* F, double* Eelec, double* pairvec, cudaStream_t st) {
+  prof_mark("fock_pair", st);
   if (t.ncls[2] > 0) {
     fock_pair_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, w.wXX, P, M, active, F, pairvec);
     SEQM_CHECK_LAUNCH("fock_pair_kernel<XX>");
@@ -206,14 +207,17 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
     fock_pair_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, w.wHH, P, M, active, F, pairvec);
     SEQM_CHECK_LAUNCH("fock_pair_kernel<HH>");
   }
+  prof_mark("fock_diag", st);
   if (t.natoms > 0) {
     fock_diag_kernel<<<cdiv(t.natoms * 32, 256), 256, 0, st>>>(t, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, active, pairvec, F);
     SEQM_CHECK_LAUNCH("fock_diag_kernel");
   }
+  prof_mark("elec_energy", st);
   if (Eelec && t.nmol > 0) {
     elec_energy_kernel<<<(unsigned)t.nmol, 256, 0, st>>>((int)t.molsize, P, F, M, nullptr, 0, active, Eelec);
     SEQM_CHECK_LAUNCH("elec_energy_kernel");
   }
+  prof_mark("end", st);
   return SEQM_OK;
 }
 

@@ -6,6 +6,9 @@
 // reference: seqm/seqm_functions/hcore.py:6-167, two_elec_two_center_int.py:7-878,
 //            two_elec_two_center_int_local_frame.py:18-281, diat_overlap.py:3-393, cal_par.py:8-173,
 //            energy.py:38-78; adjoint = what autograd replays for basics.py:369-388.
+#include <map>
+#include <vector>
+
 #include "abi_common.cuh"
 #include "pair_math.cuh"
 
@@ -13,6 +16,19 @@ namespace seqm {
 
 thread_local std::string g_last_error;
 void set_error(const std::string& s) { g_last_error = s; }
+
+unsigned long long g_launches = 0;
+static bool g_prof_on = false;
+struct ProfMark { std::string name; cudaEvent_t ev; };
+static std::vector<ProfMark> g_marks;
+void prof_mark(const char* name, cudaStream_t st) {
+  if (!g_prof_on) return;
+  ProfMark m;
+  m.name = name;
+  cudaEventCreate(&m.ev);
+  cudaEventRecord(m.ev, st);
+  g_marks.push_back(m);
+}
 
 __constant__ double c_tore[19] = {0, 1, 0, 1, 2, 3, 4, 5, 6, 7, 0, 1, 2, 3, 4, 5, 6, 7, 0};
 __constant__ double c_qn[19] = {0, 1, 0, 2, 2, 2, 2, 2, 2, 2, 0, 3, 3, 3, 3, 3, 3, 3, 0};
@@ -371,6 +387,36 @@ using namespace seqm;
 extern "C" {
 
 const char* seqm_last_error(void) { return g_last_error.c_str(); }
+
+unsigned long long seqm_launch_count(void) { return g_launches; }
+
+void seqm_profile_enable(int on) {
+  for (auto& m : g_marks) cudaEventDestroy(m.ev);
+  g_marks.clear();
+  g_prof_on = on != 0;
+}
+
+// "name total_ms count\n" per region name; synchronises the device
+int seqm_profile_report(char* buf, size_t cap) {
+  cudaDeviceSynchronize();
+  std::map<std::string, std::pair<double, int>> acc;
+  for (size_t i = 0; i + 1 < g_marks.size(); ++i) {
+    if (g_marks[i].name == "end") continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_marks[i].ev, g_marks[i + 1].ev) != cudaSuccess) { cudaGetLastError(); continue; }
+    auto& a = acc[g_marks[i].name];
+    a.first += ms;
+    a.second += 1;
+  }
+  std::string out;
+  for (auto& kv : acc) {
+    char line[256];
+    snprintf(line, sizeof line, "%s %.6f %d\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+  if (buf && cap) { snprintf(buf, cap, "%s", out.c_str()); }
+  return (int)out.size();
+}
 int seqm_version(void) { return 100; }
 size_t seqm_atompar_bytes(void) { return sizeof(AtomPar); }
 
@@ -398,6 +444,7 @@ int seqm_hcore(const seqm_topology_t* topo, const void* atompar, const double* x
   const seqm_topology_t& t = *topo;
   cudaStream_t st = (cudaStream_t)stream;
   const AtomPar* ap = (const AtomPar*)atompar;
+  prof_mark("pair_fwd", st);
   if (t.ncls[SEQM_CLS_XX] > 0) {
     SEQM_REQUIRE(w.wXX, "seqm_hcore: wXX null");
     pair_fwd_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wXX, M, EnucAB, pairvec);
@@ -413,10 +460,12 @@ int seqm_hcore(const seqm_topology_t* topo, const void* atompar, const double* x
     pair_fwd_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wHH, M, EnucAB, pairvec);
     SEQM_CHECK_LAUNCH("pair_fwd_kernel<HH>");
   }
+  prof_mark("hcore_diag", st);
   if (t.natoms > 0) {
     hcore_diag_kernel<<<cdiv(t.natoms * 32, 256), 256, 0, st>>>(t, ap, pairvec, U_ss, U_pp, M);
     SEQM_CHECK_LAUNCH("hcore_diag_kernel");
   }
+  prof_mark("end", st);
   return SEQM_OK;
 }
 
@@ -435,6 +484,7 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
   const seqm_topology_t& t = *topo;
   cudaStream_t st = (cudaStream_t)stream;
   const AtomPar* ap = (const AtomPar*)atompar;
+  prof_mark("pair_grad", st);
   if (t.ncls[2] > 0) {
     pair_grad_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
     SEQM_CHECK_LAUNCH("pair_grad_kernel<XX>");
@@ -447,6 +497,7 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
     pair_grad_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
     SEQM_CHECK_LAUNCH("pair_grad_kernel<HH>");
   }
+  prof_mark("end", st);
   return SEQM_OK;
 }
 

@@ -242,6 +242,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   uint8_t* nc = notconverged;
   int rc;
 
+  prof_mark("scf_setup", st);
   SEQM_CUDA(cudaMemsetAsync(wk.Pnew, 0, (size_t)B * nn * 8, st));
   SEQM_CUDA(cudaMemsetAsync(wk.Pold, 0, (size_t)B * nn * 8, st));
   SEQM_CUDA(cudaMemsetAsync(F, 0, (size_t)B * nn * 8, st));
@@ -270,11 +271,13 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
       counter = (counter + 1) % NFOCK;
       r = launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st);
       if (r) return r;
+      prof_mark("pulay_store", st);
       pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
       SEQM_CHECK_LAUNCH("pulay_store_kernel");
       pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
       SEQM_CHECK_LAUNCH("pulay_emat_kernel");
     }
+    prof_mark("finish+host_sync", st);
     SEQM_CUDA(cudaMemsetAsync(wk.stat, 0, 16, st));
     finish_step_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, opt->eps, wk.Enew, Eelec, wk.err, nc, niter, wk.stat);
     SEQM_CHECK_LAUNCH("finish_step_kernel");
@@ -292,6 +295,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     return SEQM_OK;
   };
   auto mix = [&](int mode) -> int {
+    prof_mark("mix", st);
     mix_kernel<<<B, 256, 0, st>>>(n4, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold);
     SEQM_CHECK_LAUNCH("mix_kernel");
     return SEQM_OK;
@@ -332,6 +336,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
         cF = cF < NFOCK ? cF + 1 : NFOCK;
         counter = (counter + 1) % NFOCK;
         SEQM_TRY(launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st));
+        prof_mark("pulay_store", st);
         pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
         pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
         { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay store: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
@@ -339,6 +344,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
         SEQM_TRY(refock_and_finish(false, counter, cF));
       }
       while (left > 0) {
+        prof_mark("pulay_extrapolate", st);
         pulay_extrapolate_kernel<<<B, 256, 0, st>>>(n4, counter, cF, nc, wk.EMAT, wk.FOCK, F);
         { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
         SEQM_TRY(density(P));
@@ -347,6 +353,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
       }
     }
   }
+  prof_mark("end", st);
   cudaFreeHost(hstat);
   if (iterations_out) *iterations_out = k;
   return SEQM_OK;

@@ -197,6 +197,7 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   uint8_t* live = (uint8_t*)base; base += al256(nmol);
   uint8_t* took = (uint8_t*)base; base += al256(nmol);
   int* nlive = (int*)base;
+  prof_mark("sp2_init", st);
   sp2_init_kernel<<<B, 256, 0, st>>>(S, ld, F, nheavy, nhydro, nocc, active, X, state, dims);
   SEQM_CHECK_LAUNCH("sp2_init_kernel");
   sp2_sync_live_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, state, live);
@@ -211,6 +212,7 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   for (int it = 0; it < 200; ++it) {
     rc = launch_dgemm_batched(ld, ld, X, X, X2, stride, B, live, dims, st);
     if (rc) break;
+    prof_mark("sp2_update+host_sync", st);
     cudaMemsetAsync(nlive, 0, sizeof(int), st);
     cudaMemcpyAsync(took, live, B, cudaMemcpyDeviceToDevice, st);
     sp2_decide_kernel<<<B, 256, 0, st>>>(ld, eps, dims, X, X2, state, live, nlive);
@@ -225,8 +227,10 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   if (rc) return rc;
   int fchunks = (int)(((long long)mmax * mmax + 255) / 256);
   if (fchunks > 512) fchunks = 512;
+  prof_mark("sp2_finish", st);
   sp2_finish_kernel<<<dim3(fchunks, B), 256, 0, st>>>(S, ld, X, nheavy, dims, active, state, D, niter);
   SEQM_CHECK_LAUNCH("sp2_finish_kernel");
+  prof_mark("end", st);
   return SEQM_OK;
 }
 
