@@ -16,6 +16,7 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
 
 int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                         const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
-                        double* e_out, double* v_out, int32_t* info, cudaStream_t st);
+                        double* e_out, double* v_out, int32_t* info, double* Vstore, int warm, cudaStream_t st);
+size_t eigh_vstore_doubles(int64_t nmol, int mmax);
 
 }  // namespace seqm

@@ -1,16 +1,19 @@
 // K3a: batched symmetric eigensolver + density, one CTA per molecule, everything in shared memory.
-//   pack (pack.py:7-21) -> parallel-order cyclic Jacobi (two-sided, tournament schedule: every round
-//   rotates m/2 disjoint index pairs, each thread owns 2x2 tiles so a round needs two barriers) ->
-//   rank sort of the eigenvalues -> P = 2 C_occ C_occ^T -> unpack (pack.py:34-41) to the padded layout.
+//   pack (pack.py:7-21) -> [warm start: A <- V0^T A V0 with the eigenvectors of the previous SCF iteration]
+//   -> parallel-order cyclic Jacobi (two-sided, tournament schedule: every round rotates m/2 disjoint index
+//   pairs, each thread owns 2x2 tiles so a round needs two barriers) -> rank sort of the eigenvalues ->
+//   P = 2 C_occ C_occ^T -> unpack (pack.py:34-41) to the padded layout.
 // Works on the PACKED matrix (m = 4 nHeavy + nHydro), so the reference's trick of pushing the padding
 // rows above the spectrum (diag.py:116-130) is not needed; orbital energies are returned zero padded like
-// diag.py:140-144.
+// diag.py:140-144.  The warm start does not change the result (the decomposition is still converged to
+// 1e-14 of the norm); it cuts the sweeps from ~9 to 2-3 because consecutive Fock matrices are close.
 // reference: seqm/seqm_functions/diag.py:102-172
 #include "abi_common.cuh"
 
 namespace seqm {
 
 constexpr int EIGH_MAX_M = 118;
+constexpr int EIGH_WARM_MAX_M = 96;     // three m x m buffers must fit in shared memory for the warm start
 constexpr int EIGH_MAX_SWEEPS = 40;
 
 __device__ __forceinline__ int packed_to_padded(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
@@ -27,31 +30,36 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return s;
 }
 
-__global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
-                                    const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
-                                    const uint8_t* __restrict__ active, double* __restrict__ P,
-                                    double* __restrict__ e_out, double* __restrict__ v_out,
-                                    int32_t* __restrict__ info) {
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
+                    const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
+                    const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
+                    double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore,
+                    int warm) {
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const int nh4 = 4 * nheavy[mol];
   const int m = nh4 + nhydro[mol];
   const int n4 = 4 * S;
   const size_t base = (size_t)mol * n4 * n4;
-  const int tid = threadIdx.x, nt = blockDim.x;
+  const int tid = threadIdx.x;
   if (m <= 0) return;
   const int mp = (m + 1) & ~1;      // even size for the tournament; the extra index never couples
   const int ld = mp + 1;
   extern __shared__ double sm[];
-  double* A = sm;                          // [mp][ld]
-  double* V = A + (size_t)ldmax * (ldmax + 1);   // [mp][ld]
-  double* cs = V + (size_t)ldmax * (ldmax + 1);  // [mp/2][2]
-  double* red = cs + ldmax;                // [32]
-  int* pq = (int*)(red + 32);              // [mp/2][2]
-  int* rank = pq + ldmax;                  // [mp]
-  int* occ = rank + ldmax;                 // [mp]
+  const size_t mat = (size_t)ldmax * (ldmax + 1);
+  double* A = sm;                   // [mp][ld]
+  double* V = A + mat;              // [mp][ld]
+  double* T = V + mat;              // [mp][ld] only when Vstore != nullptr
+  double* cs = Vstore ? T + mat : T;   // [mp/2][2]
+  double* red = cs + ldmax;         // [32]
+  int* pq = (int*)(red + 32);       // [mp/2][2]
+  int* rank = pq + ldmax;           // [mp]
+  int* occ = rank + ldmax;          // [mp]
+  double* Vg = Vstore ? Vstore + (size_t)mol * ldmax * ldmax : nullptr;
 
-  for (int idx = tid; idx < mp * mp; idx += nt) {
+  for (int idx = tid; idx < mp * mp; idx += NT) {
     const int i = idx / mp, j = idx - i * mp;
     double a = 0.0;
     if (i < m && j < m) {
@@ -59,17 +67,37 @@ __global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__
       a = F[base + (size_t)packed_to_padded(r, nh4) * n4 + packed_to_padded(c, nh4)];
     }
     A[i * ld + j] = a;
-    V[i * ld + j] = (i == j) ? 1.0 : 0.0;
+    double v = (i == j) ? 1.0 : 0.0;
+    if (warm && Vg && i < m && j < m) v = Vg[i * m + j];
+    V[i * ld + j] = v;
   }
   __syncthreads();
+  if (warm && Vg) {
+    // T = A V ; A = V^T T   (upper triangle computed, mirrored)
+    for (int idx = tid; idx < m * m; idx += NT) {
+      const int i = idx / m, j = idx - i * m;
+      double acc = 0.0;
+      for (int k = 0; k < m; ++k) acc += A[i * ld + k] * V[k * ld + j];
+      T[i * ld + j] = acc;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < m * m; idx += NT) {
+      const int i = idx / m, j = idx - i * m;
+      if (i > j) continue;
+      double acc = 0.0;
+      for (int k = 0; k < m; ++k) acc += V[k * ld + i] * T[k * ld + j];
+      A[i * ld + j] = acc;
+      A[j * ld + i] = acc;
+    }
+    __syncthreads();
+  }
 
   const int half = mp >> 1;
   int sweeps = 0;
   bool last = false;
   for (; sweeps < EIGH_MAX_SWEEPS; ++sweeps) {
-    // off-diagonal and total norms
     double off = 0.0, tot = 0.0;
-    for (int idx = tid; idx < mp * mp; idx += nt) {
+    for (int idx = tid; idx < mp * mp; idx += NT) {
       const int i = idx / mp, j = idx - i * mp;
       const double a = A[i * ld + j];
       tot += a * a;
@@ -88,9 +116,10 @@ __global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__
         const double apq = A[p * ld + q];
         double c = 1.0, s = 0.0;
         if (apq != 0.0) {
-          const double theta = (A[q * ld + q] - A[p * ld + p]) / (2.0 * apq);
-          const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-          c = 1.0 / sqrt(tt * tt + 1.0);
+          // t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)), theta = (aqq - app) / (2 apq), without forming theta
+          const double d = A[q * ld + q] - A[p * ld + p], b = 2.0 * apq;
+          const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) / (fabs(d) + sqrt(d * d + b * b));
+          c = rsqrt(tt * tt + 1.0);
           s = tt * c;
         }
         cs[2 * tid] = c; cs[2 * tid + 1] = s;
@@ -98,37 +127,39 @@ __global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__
       }
       __syncthreads();
       const int nblk = half * half;
-      for (int task = tid; task < nblk + mp * half; task += nt) {
+      for (int task = tid; task < nblk + mp * half; task += NT) {
         if (task < nblk) {
           const int ka = task / half, kb = task - ka * half;
-          const int pa = pq[2 * ka], qa = pq[2 * ka + 1], pb = pq[2 * kb], qb = pq[2 * kb + 1];
-          const double ca = cs[2 * ka], sa = cs[2 * ka + 1], cb = cs[2 * kb], sb = cs[2 * kb + 1];
+          const int2 ra = *reinterpret_cast<const int2*>(pq + 2 * ka), rb = *reinterpret_cast<const int2*>(pq + 2 * kb);
+          const double2 ja = *reinterpret_cast<const double2*>(cs + 2 * ka), jb = *reinterpret_cast<const double2*>(cs + 2 * kb);
+          const int pa = ra.x, qa = ra.y, pb = rb.x, qb = rb.y;
+          const double ca = ja.x, sa = ja.y, cb = jb.x, sb = jb.y;
           const double a00 = A[pa * ld + pb], a01 = A[pa * ld + qb], a10 = A[qa * ld + pb], a11 = A[qa * ld + qb];
-          // rows: J_a^T * blk
-          const double b00 = ca * a00 - sa * a10, b01 = ca * a01 - sa * a11;
+          const double b00 = ca * a00 - sa * a10, b01 = ca * a01 - sa * a11;      // rows: J_a^T blk
           const double b10 = sa * a00 + ca * a10, b11 = sa * a01 + ca * a11;
-          // columns: * J_b
-          double c00 = cb * b00 - sb * b01, c01 = sb * b00 + cb * b01;
+          double c00 = cb * b00 - sb * b01, c01 = sb * b00 + cb * b01;            // columns: blk J_b
           double c10 = cb * b10 - sb * b11, c11 = sb * b10 + cb * b11;
           if (ka == kb) { c01 = 0.0; c10 = 0.0; }
           A[pa * ld + pb] = c00; A[pa * ld + qb] = c01; A[qa * ld + pb] = c10; A[qa * ld + qb] = c11;
         } else {
           const int t2 = task - nblk;
           const int i = t2 / half, kb = t2 - i * half;
-          const int pb = pq[2 * kb], qb = pq[2 * kb + 1];
-          const double cb = cs[2 * kb], sb = cs[2 * kb + 1];
-          const double v0 = V[i * ld + pb], v1 = V[i * ld + qb];
-          V[i * ld + pb] = cb * v0 - sb * v1;
-          V[i * ld + qb] = sb * v0 + cb * v1;
+          const int2 rb = *reinterpret_cast<const int2*>(pq + 2 * kb);
+          const double2 jb = *reinterpret_cast<const double2*>(cs + 2 * kb);
+          const double v0 = V[i * ld + rb.x], v1 = V[i * ld + rb.y];
+          V[i * ld + rb.x] = jb.x * v0 - jb.y * v1;
+          V[i * ld + rb.y] = jb.y * v0 + jb.x * v1;
         }
       }
       __syncthreads();
     }
   }
   if (info && tid == 0) info[mol] = sweeps;
+  if (Vg)
+    for (int idx = tid; idx < m * m; idx += NT) Vg[idx] = V[(idx / m) * ld + (idx % m)];
 
   // rank of every eigenvalue (ascending, ties by index: a stable sort)
-  for (int i = tid; i < m; i += nt) {
+  for (int i = tid; i < m; i += NT) {
     const double ei = A[i * ld + i];
     int rk = 0;
     for (int j = 0; j < m; ++j) {
@@ -139,15 +170,14 @@ __global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__
   }
   __syncthreads();
   const int no = nocc[mol];
-  for (int i = tid; i < m; i += nt) {
+  for (int i = tid; i < m; i += NT) {
     if (rank[i] < no) occ[rank[i]] = i;
     if (e_out) e_out[(size_t)mol * n4 + rank[i]] = A[i * ld + i];
   }
   if (e_out)
-    for (int i = m + tid; i < n4; i += nt) e_out[(size_t)mol * n4 + i] = 0.0;
+    for (int i = m + tid; i < n4; i += NT) e_out[(size_t)mol * n4 + i] = 0.0;
   if (v_out) {
-    // eigenvectors as columns in ascending order, packed rows: v[i][rank]
-    for (int idx = tid; idx < m * m; idx += nt) {
+    for (int idx = tid; idx < m * m; idx += NT) {
       const int i = idx / m, k = idx - i * m;
       v_out[base + (size_t)i * n4 + rank[k]] = V[i * ld + k];
     }
@@ -155,47 +185,67 @@ __global__ void eigh_density_kernel(int S, int ldmax, const double* __restrict__
   __syncthreads();
   // occupied coefficient block C[i][k] into A (the rotated matrix is no longer needed)
   const int nocc_c = no < m ? no : m;
-  for (int idx = tid; idx < m * nocc_c; idx += nt) {
+  for (int idx = tid; idx < m * nocc_c; idx += NT) {
     const int i = idx / nocc_c, k = idx - i * nocc_c;
     A[i * ld + k] = V[i * ld + occ[k]];
   }
   __syncthreads();
-  for (int idx = tid; idx < m * m; idx += nt) {
+  for (int idx = tid; idx < m * m; idx += NT) {
     const int i = idx / m, j = idx - i * m;
-    const int r = i <= j ? i : j, c = i <= j ? j : i;     // same operand order for (i,j) and (j,i)
+    if (i > j) continue;
     double acc = 0.0;
-    for (int k = 0; k < nocc_c; ++k) acc += A[r * ld + k] * A[c * ld + k];
-    P[base + (size_t)packed_to_padded(i, nh4) * n4 + packed_to_padded(j, nh4)] = 2.0 * acc;
+    for (int k = 0; k < nocc_c; ++k) acc += A[i * ld + k] * A[j * ld + k];
+    acc *= 2.0;
+    P[base + (size_t)packed_to_padded(i, nh4) * n4 + packed_to_padded(j, nh4)] = acc;
+    P[base + (size_t)packed_to_padded(j, nh4) * n4 + packed_to_padded(i, nh4)] = acc;
   }
 }
 
-size_t eigh_smem_bytes(int mmax) {
-  const int mp = (mmax + 1) & ~1;
-  return ((size_t)2 * mp * (mp + 1) + mp + 32) * sizeof(double) + (size_t)3 * mp * sizeof(int) + 64;
+static size_t eigh_smem_bytes(int mp, bool warm) {
+  return ((size_t)(warm ? 3 : 2) * mp * (mp + 1) + mp + 32) * sizeof(double) + (size_t)3 * mp * sizeof(int) + 64;
 }
 
+size_t eigh_vstore_doubles(int64_t nmol, int mmax) {
+  const int mp = (mmax + 1) & ~1;
+  return mmax <= EIGH_WARM_MAX_M ? (size_t)nmol * mp * mp : 0;
+}
+
+template <int NT, int MINB>
+static int launch_cfg(int64_t nmol, size_t smem, cudaStream_t st, int S, int mp, const double* F, const int32_t* nheavy,
+                      const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
+                      double* v_out, int32_t* info, double* Vstore, int warm) {
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  eigh_density_kernel<NT, MINB><<<(unsigned)nmol, NT, smem, st>>>(S, mp, F, nheavy, nhydro, nocc, active, P, e_out,
+                                                                  v_out, info, Vstore, warm);
+  SEQM_CHECK_LAUNCH("eigh_density_kernel");
+  return SEQM_OK;
+}
+
+// Vstore: nullptr (cold start every call) or eigh_vstore_doubles() doubles kept by the caller between calls;
+// warm != 0 starts from the eigenvectors stored there by the previous call
 int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                         const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
-                        double* e_out, double* v_out, int32_t* info, cudaStream_t st) {
+                        double* e_out, double* v_out, int32_t* info, double* Vstore, int warm, cudaStream_t st) {
   if (nmol == 0) return SEQM_OK;
   if (mmax > EIGH_MAX_M) return fail(SEQM_EUNSUPPORTED, "seqm_eigh_density: packed size above the shared-memory Jacobi limit (118); use the SP2 density path");
   if (mmax < 1) mmax = 1;
+  if (mmax > EIGH_WARM_MAX_M) { Vstore = nullptr; warm = 0; }
   const int mp = (mmax + 1) & ~1;
-  const size_t smem = eigh_smem_bytes(mmax);
-  int threads = ((3 * mp * mp / 4) / 2 + 31) / 32 * 32;
-  if (threads < 64) threads = 64;
-  if (threads > 1024) threads = 1024;
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  const size_t smem = eigh_smem_bytes(mp, Vstore != nullptr);
   prof_mark("eigh_density", st);
-  eigh_density_kernel<<<(unsigned)nmol, threads, smem, st>>>((int)molsize, mp, F, nheavy, nhydro, nocc, active, P,
-                                                           e_out, v_out, info);
-  SEQM_CHECK_LAUNCH("eigh_density_kernel");
+  int rc;
+  if (mp <= 32)
+    rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
+  else if (mp <= 64)
+    rc = launch_cfg<512, 2>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
+  else
+    rc = launch_cfg<1024, 1>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
   prof_mark("end", st);
-  return SEQM_OK;
+  return rc;
 }
 
 }  // namespace seqm
@@ -210,7 +260,7 @@ int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, 
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
                       double* v_out, int32_t* info, void* stream) {
   SEQM_REQUIRE(F && nheavy && nhydro && nocc && P && nmol >= 0 && molsize > 0, "seqm_eigh_density: bad argument");
-  return launch_eigh_density(nmol, molsize, mmax, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info,
+  return launch_eigh_density(nmol, molsize, mmax, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, nullptr, 0,
                              (cudaStream_t)stream);
 }
 

@@ -184,7 +184,7 @@ __global__ void init_flags_kernel(int nmol, uint8_t* nc, double* err, int32_t* n
 }
 
 struct ScfWork {
-  double *Pnew, *Pold, *Enew, *err, *G, *FOCK, *FPPF, *EMAT;
+  double *Pnew, *Pold, *Enew, *err, *G, *FOCK, *FPPF, *EMAT, *Vstore;
   unsigned long long* stat;
   char* sp2;
   size_t total;
@@ -209,6 +209,7 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
     w.EMAT = (double*)take(nmol * 36 * 8);
   }
   if (opt->use_sp2) w.sp2 = take(seqm_sp2_workspace(nmol, molsize));
+  else w.Vstore = (double*)take((size_t)nmol * 16 * molsize * molsize * 8);
   w.total = off;
   return w;
 }
@@ -258,10 +259,13 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   long long left = B;
   const int max_iter = opt->max_iter > 0 ? opt->max_iter : 1000;
 
+  int ncalls_density = 0;
   auto density = [&](double* out) -> int {
     if (opt->use_sp2)
       return seqm_sp2_density(B, S, mmax, F, nheavy, nhydro, nocc, opt->sp2_eps, nc, out, nullptr, wk.sp2, st);
-    return launch_eigh_density(B, S, mmax, F, nheavy, nhydro, nocc, nc, out, nullptr, nullptr, nullptr, st);
+    const int warm = ncalls_density > 0 ? 1 : 0;
+    ++ncalls_density;
+    return launch_eigh_density(B, S, mmax, F, nheavy, nhydro, nocc, nc, out, nullptr, nullptr, nullptr, wk.Vstore, warm, st);
   };
   auto refock_and_finish = [&](bool store, int& counter, int& cF) -> int {
     int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, st);
