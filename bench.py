@@ -38,26 +38,36 @@ def peaks():
         return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons while the timed region runs"""
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs: ONE long-running nvidia-smi process
+    (-lms 200) started before the timed region and stopped after it."""
 
     def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.proc, self.rows = index, None, []
 
-    def run(self):
+    def start(self):
         q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
-                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
-                t = [x.strip() for x in out.strip().split(',')]
-                if len(t) >= 6:
-                    self.rows.append(t)
-            except Exception:
-                pass
-            time.sleep(0.15)
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
+                                          '--format=csv,noheader,nounits', '-lms', '200'], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ''
+        for line in out.strip().splitlines():
+            t = [x.strip() for x in line.split(',')]
+            if len(t) >= 6:
+                self.rows.append(t)
 
     def summary(self):
         if not self.rows:
@@ -198,7 +208,8 @@ def run_gpu(args, rank, world, local_rank):
         e_host.copy_(o[2].detach(), non_blocking=True)
         torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
-    sampler.stop_flag = True
+    if rank == 0:
+        sampler.stop()
     t = torch.tensor([total_ms, e2e_ms], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -209,7 +220,7 @@ def run_gpu(args, rank, world, local_rank):
         return
     # ---- per-kernel profile of one step, and the kernels timed alone on the converged state ----
     L.seqm_profile_enable(1)
-    step(coords.clone())
+    force_mod(const, coords.clone(), species)        # no collective here: the other ranks have finished
     buf = ctypes.create_string_buffer(1 << 16)
     L.seqm_profile_report(buf, len(buf))
     L.seqm_profile_enable(0)

@@ -127,6 +127,7 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  *   v_out[B][n][n] (may be NULL) eigenvectors in the reference's packed layout C[packed orbital][k];
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
+void seqm_eigh_force_block(int on); /* test hook: shared-memory (CTA) Jacobi also for m <= 32 */
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                       double* e_out, double* v_out, int32_t* info, void* stream);

@@ -53,6 +53,8 @@ def lib():
         L.seqm_profile_report.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
         L.seqm_atompar_bytes.restype = ctypes.c_size_t
         L.seqm_eigh_max_m.restype = ctypes.c_int
+        L.seqm_eigh_force_block.argtypes = [ctypes.c_int]
+        L.seqm_eigh_force_block.restype = None
         L.seqm_sp2_workspace.restype = ctypes.c_size_t
         L.seqm_sp2_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64]
         L.seqm_scf_workspace.restype = ctypes.c_size_t
@@ -73,14 +75,14 @@ def lib():
         for name in EXPORTS:
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
-                            'seqm_launch_count', 'seqm_profile_enable'):
+                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block'):
                 fn.restype = ctypes.c_int
         _lib = L
     return _lib
 
 
 EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
-           'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_density', 'seqm_sp2_workspace',
+           'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_density', 'seqm_sp2_workspace',
            'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched']
 
 

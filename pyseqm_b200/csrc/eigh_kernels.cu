@@ -9,6 +9,7 @@
 // 1e-14 of the norm); it cuts the sweeps from ~9 to 2-3 because consecutive Fock matrices are close.
 // reference: seqm/seqm_functions/diag.py:102-172
 #include "abi_common.cuh"
+#include "dgemm.cuh"
 
 namespace seqm {
 
@@ -201,6 +202,8 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
   }
 }
 
+int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
+
 static size_t eigh_smem_bytes(int mp, bool warm) {
   return ((size_t)(warm ? 3 : 2) * mp * (mp + 1) + mp + 32) * sizeof(double) + (size_t)3 * mp * sizeof(int) + 64;
 }
@@ -238,7 +241,9 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   const size_t smem = eigh_smem_bytes(mp, Vstore != nullptr);
   prof_mark("eigh_density", st);
   int rc;
-  if (mp <= 32)
+  if (mp <= 32 && !g_force_block_jacobi)
+    rc = launch_eigh_warp(nmol, molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, st);
+  else if (mp <= 32)
     rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
   else if (mp <= 64)
     rc = launch_cfg<512, 2>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
@@ -255,6 +260,7 @@ using namespace seqm;
 extern "C" {
 
 int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
+void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
 
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,

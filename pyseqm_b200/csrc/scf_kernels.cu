@@ -209,7 +209,7 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
     w.EMAT = (double*)take(nmol * 36 * 8);
   }
   if (opt->use_sp2) w.sp2 = take(seqm_sp2_workspace(nmol, molsize));
-  else w.Vstore = (double*)take((size_t)nmol * 16 * molsize * molsize * 8);
+  else w.Vstore = (double*)take((size_t)nmol * (16 * molsize * molsize > 1024 ? 16 * molsize * molsize : 1024) * 8);
   w.total = off;
   return w;
 }

@@ -52,6 +52,46 @@ def test_dgemm_matches_matmul():
         assert float((C - ref).abs().max()) < 1e-11 * n, n
 
 
+@pytest.mark.parametrize('force_block', [0, 1])
+def test_eigh_kernels_random(force_block):
+    """warp-register Jacobi (m <= 32) and shared-memory CTA Jacobi against LAPACK on random symmetric matrices of
+    mixed sizes (odd sizes, hydrogens only, one orbital, full 32)"""
+    from pyseqm_b200 import _lib, _ops
+    import seqm_oracle as orc
+    dev = _dev()
+    rng = np.random.RandomState(3)
+    shapes = [(7, 4), (0, 1), (0, 2), (1, 0), (8, 0), (6, 6), (3, 5), (0, 7), (2, 23), (5, 11), (4, 13)]
+    if force_block:
+        shapes += [(12, 10), (20, 16), (24, 22)]
+    S = max(a + b for a, b in shapes)
+    n4 = 4 * S
+    B = len(shapes)
+    nH = torch.tensor([a for a, b in shapes]); nh = torch.tensor([b for a, b in shapes])
+    nocc = torch.tensor([max(1, (4 * a + b) // 2) for a, b in shapes])
+    F = torch.zeros(B, n4, n4)
+    for b_, (a, h) in enumerate(shapes):
+        m = 4 * a + h
+        X = torch.as_tensor(rng.standard_normal((m, m))); X = X + X.T
+        Fp = torch.zeros(1, m, m); Fp[0] = X
+        F[b_] = orc.unpack(Fp, nH[b_:b_ + 1], nh[b_:b_ + 1], n4)[0]
+    Pref, eref, _ = orc.density_eigh(F, nH, nh, nocc, want_eig=True)
+    mmax = int((4 * nH + nh).max())
+    i32 = torch.int32
+    _lib.lib().seqm_eigh_force_block(force_block)
+    try:
+        P, e, v = _ops.eigh_density(F.to(dev), nH.to(dev).to(i32), nh.to(dev).to(i32), nocc.to(dev).to(i32), S, mmax,
+                                    want_eig=True)
+    finally:
+        _lib.lib().seqm_eigh_force_block(0)
+    assert float((e.cpu() - eref).abs().max()) < 1e-12
+    assert float((P.cpu() - Pref).abs().max()) < 1e-11
+    assert float((P - P.transpose(1, 2)).abs().max()) == 0.0
+    for b_, (a, h) in enumerate(shapes):
+        m = 4 * a + h
+        C = v[b_, :m, :m].cpu()
+        assert float((C.T @ C - torch.eye(m)).abs().max()) < 1e-13
+
+
 @pytest.mark.parametrize('name', golden_names())
 def test_hcore_fock_density_ops(name):
     """op-level parity on the reference's own intermediate tensors"""
