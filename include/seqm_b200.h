@@ -89,6 +89,14 @@ int seqm_atom_pack(int64_t natoms, const int32_t* Z, const double* zeta_s, const
                    const double* g_p2, const double* h_sp, const double* alpha, const double* gK,
                    const double* gL, const double* gM, int ngauss, void* atompar_out, void* stream);
 
+/* Pair geometry of the Parser (reference basics.py:91-108) on the device: R[B][S][3] (Angstrom) ->
+ * xij[P][3] = (R_j - R_i)/d, rij[P] = d*lcf (zero distance^2 -> 1e-4), and its adjoint:
+ * gR[B][S][3] (must be zero filled: padding atoms are not written) from gx[P][3], gr[P]. */
+int seqm_pair_geometry(const seqm_topology_t* topo, const double* R, double lcf, double* xij, double* rij,
+                       void* stream);
+int seqm_pair_geometry_grad(const seqm_topology_t* topo, const double* xij, const double* rij, const double* gx,
+                            const double* gr, double lcf, double* gR, void* stream);
+
 /* hcore() (reference hcore.py:6-167) = two-centre integrals + rotate + diatomic overlap + core
  * Hamiltonian, and pair_nuclear_energy() (energy.py:38-78).
  *   xij[P][3], rij[P]      Parser geometry (unit vector i->j, distance in bohr)
@@ -128,6 +136,7 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
 void seqm_eigh_force_block(int on); /* test hook: shared-memory (CTA) Jacobi also for m <= 32 */
+void seqm_eigh_tolerance(double tol); /* Jacobi stopping rule: one final sweep once off^2 <= tol * total^2 (default 1e-24) */
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                       double* e_out, double* v_out, int32_t* info, void* stream);
@@ -144,6 +153,7 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
  *   converger: 0 constant mixing (alpha), 1 adaptive, 2 adaptive then Pulay
  *   P[B][n][n] in: initial guess, out: converged density; F out: fock(P) at the final density
  *   notconverged[B] out; niter[B] out (iterations taken by each molecule)
+ *   iterations_out: int32[2] on the HOST = {iterations run, molecules still unconverged}
  *   work: seqm_scf_workspace(...) bytes.  Synchronises the stream once per iteration (convergence
  *   count), like the reference's notconverged.any(). */
 typedef struct {

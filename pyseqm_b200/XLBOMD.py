@@ -30,14 +30,25 @@ class EnergyXL(torch.nn.Module):
     def forward(self, const, coordinates, species, P, learned_parameters=dict(), all_terms=False, step=0, *args,
                 **kwargs):
         """P: dynamical field density; D: density from F(P) (SP2 / eigh), returned last"""
-        nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
-            self.parser(const, species, coordinates, *args, **kwargs)
-        if callable(learned_parameters):
-            parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
+        prep = _engine.prepared_for(const, self.parser, self.packpar, species, coordinates, self.method,
+                                    learned_parameters, kwargs)
+        if prep is not None:
+            nmol, molsize, nHeavy, nHydro, nocc, Z, maskd = prep.nmol, prep.molsize, prep.nHeavy, prep.nHydro, \
+                prep.nocc, prep.Z, prep.maskd
+            atom_molid, pair_molid, idxi, idxj, parameters = prep.atom_molid, prep.pair_molid, prep.idxi, prep.idxj, \
+                prep.parameters
+            xij, rij = _ops.PairGeometry.apply(coordinates, prep.topo, prep.lcf)
+            st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
+                               self.method, run_scf=False, topo=prep.topo, atompar=prep.atompar)
         else:
-            parameters = self.packpar(Z, learned_params=learned_parameters)
-        st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
-                           self.method, run_scf=False)
+            nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
+                self.parser(const, species, coordinates, *args, **kwargs)
+            if callable(learned_parameters):
+                parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
+            else:
+                parameters = self.packpar(Z, learned_params=learned_parameters)
+            st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
+                               self.method, run_scf=False)
         topo = st['topo']
         sp2 = self.seqm_parameters['sp2']
         with torch.no_grad():
@@ -54,9 +65,9 @@ class EnergyXL(torch.nn.Module):
         Eelec, EnucAB = _ops.PairEnergy.apply(xij, rij, st)
         if all_terms:
             Etot, Enuc = total_energy(nmol, pair_molid, EnucAB, Eelec)
-            Eiso = elec_energy_isolated_atom(const, Z, uss=parameters['U_ss'], upp=parameters['U_pp'],
-                                             gss=parameters['g_ss'], gpp=parameters['g_pp'], gsp=parameters['g_sp'],
-                                             gp2=parameters['g_p2'], hsp=parameters['h_sp'])
+            Eiso = prep.Eiso if prep is not None else elec_energy_isolated_atom(
+                const, Z, uss=parameters['U_ss'], upp=parameters['U_pp'], gss=parameters['g_ss'],
+                gpp=parameters['g_pp'], gsp=parameters['g_sp'], gp2=parameters['g_p2'], hsp=parameters['h_sp'])
             Hf, Eiso_sum = heat_formation(const, nmol, atom_molid, Z, Etot, Eiso, flag=self.Hf_flag)
             return Hf, Etot, Eelec, Enuc, Eiso_sum, EnucAB, D
         return Eelec, EnucAB, D

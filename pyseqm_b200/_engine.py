@@ -1,6 +1,12 @@
 """Host-side orchestration of one Hamiltonian build: topology (cached per pair list) -> per-atom records ->
 pair pass (hcore) -> device-resident SCF.  Used by seqm_functions.scf_loop.scf_loop, basics.Energy and
-XLBOMD.EnergyXL."""
+XLBOMD.EnergyXL.
+
+`Prepared` is the fast path of Energy / EnergyXL: everything that depends only on the species tensor (the
+Parser's index tensors, topology, per-atom parameters and records, the initial density guess, isolated-atom
+energies) is computed once and reused while the same species tensor comes back (MD, geometry scans); per call
+only the pair geometry (one kernel, with a kernel adjoint) is recomputed.  It applies when the pair list cannot
+change with the coordinates (pair_outer_cutoff effectively infinite) and no per-call parameters are given."""
 import time
 import warnings
 
@@ -11,11 +17,14 @@ from ._topology import PairTopology
 
 _TOPO_CACHE = []      # small LRU of (key tensors, PairTopology)
 _TOPO_CACHE_SIZE = 4
+_PREP_CACHE = []
+_PREP_CACHE_SIZE = 4
+ALL_PAIRS_CUTOFF = 1.0e6      # Angstrom: beyond any molecule, the pair list is the full a<b list
 
 
 def get_topology(nmol, molsize, Z, maskd, idxi, idxj, nHeavy, nHydro, nocc):
-    """PairTopology for these Parser tensors; reused while the pair list is unchanged (MD without cutoff
-    changes).  Validation compares the index tensors on the device (one sync)."""
+    """PairTopology for these Parser tensors; reused while the pair list is unchanged.  Validation compares
+    the index tensors on the device (one sync)."""
     for k, (cz, cm, ci, cj, co, topo) in enumerate(_TOPO_CACHE):
         if (topo.nmol == nmol and topo.molsize == molsize and cz.shape == Z.shape and ci.shape == idxi.shape
                 and cz.device == Z.device):
@@ -57,15 +66,18 @@ def _toc(const, key, t0):
 
 
 def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters, method,
-          run_scf=True, P0=None, eps=1.0e-4, sp2=(False,), scf_converger=(1,), max_iter=1000, debug=False):
+          run_scf=True, P0=None, eps=1.0e-4, sp2=(False,), scf_converger=(1,), max_iter=1000, debug=False,
+          topo=None, atompar=None, P_guess=None):
     """-> state dict: topo, atompar, w, M, EnucAB, pv and (if run_scf) P, F, Eelec, notconverged, niter"""
     for k in ('Kbeta', 'g_ss_nuc'):
         if k in parameters:
             raise NotImplementedError("parameter '%s' (learned-parameter feature) is outside the B200 hot path" % k)
-    topo = get_topology(int(nmol), int(molsize), Z, maskd, idxi, idxj, nHeavy, nHydro, nocc)
+    if topo is None:
+        topo = get_topology(int(nmol), int(molsize), Z, maskd, idxi, idxj, nHeavy, nHydro, nocc)
     t0 = _tic(const)
     with torch.no_grad():
-        atompar = _ops.atom_pack(topo, parameters, method)
+        if atompar is None:
+            atompar = _ops.atom_pack(topo, parameters, method)
         w, M, EnucAB, pv = _ops.hcore(topo, atompar, xij, rij, parameters['U_ss'], parameters['U_pp'], method)
     _toc(const, "Hcore + STO Integrals", t0)
     st = dict(topo=topo, atompar=atompar, w=w, M=M, EnucAB=EnucAB, pv=pv, method=method)
@@ -74,16 +86,61 @@ def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij,
     if run_scf:
         t0 = _tic(const)
         with torch.no_grad():
-            P = initial_density(const, topo, Z, maskd) if not torch.is_tensor(P0) else P0
-            P, F, E, nc, nit, iters = _ops.scf(topo, w, M, par5, P, float(eps), list(scf_converger), list(sp2),
-                                               max_iter, debug, pv)
+            if torch.is_tensor(P0):
+                P = P0
+            elif P_guess is not None:
+                P = P_guess
+            else:
+                P = initial_density(const, topo, Z, maskd)
+            P, F, E, nc, nit, (iters, left) = _ops.scf(topo, w, M, par5, P, float(eps), list(scf_converger), list(sp2),
+                                                       max_iter, debug, pv)
         st.update(P=P, F=F, Eelec=E, notconverged=nc, niter=nit, iterations=iters)
-        if bool(nc.any()):
-            nnot = int(nc.sum())
-            warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (nnot, nmol, max_iter))
+        if left:
+            warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (left, nmol, max_iter))
         _toc(const, "SCF", t0)
     return st
 
 
 def hcore_matrix(M, nmol, molsize):
     return M.reshape(nmol, molsize, molsize, 4, 4).transpose(2, 3).reshape(nmol, 4 * molsize, 4 * molsize)
+
+
+class Prepared:
+    """species-only data of one batch (see module docstring)"""
+
+    def __init__(self, const, parser, packpar, species, coordinates, method):
+        from .seqm_functions.energy import elec_energy_isolated_atom
+        with torch.no_grad():
+            out = parser(const, species, coordinates.detach())
+        (self.nmol, self.molsize, self.nHeavy, self.nHydro, self.nocc, self.Z, self.maskd, self.atom_molid, self.mask,
+         self.pair_molid, self.ni, self.nj, self.idxi, self.idxj, _, _) = out
+        self.species = species
+        self.key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method,
+                    id(packpar))
+        self.parameters = packpar(self.Z, learned_params=dict())
+        self.topo = PairTopology(self.nmol, self.molsize, self.Z, self.maskd, self.idxi, self.idxj, self.nHeavy,
+                                 self.nHydro, self.nocc)
+        self.atompar = _ops.atom_pack(self.topo, self.parameters, method)
+        self.P_guess = initial_density(const, self.topo, self.Z, self.maskd)
+        p = self.parameters
+        self.Eiso = elec_energy_isolated_atom(const, self.Z, uss=p['U_ss'], upp=p['U_pp'], gss=p['g_ss'],
+                                              gpp=p['g_pp'], gsp=p['g_sp'], gp2=p['g_p2'], hsp=p['h_sp'])
+        self.lcf = float(const.length_conversion_factor)
+
+
+def prepared_for(const, parser, packpar, species, coordinates, method, learned_parameters, kwargs):
+    """Prepared object if the fast path applies, else None"""
+    if kwargs or callable(learned_parameters) or len(learned_parameters) > 0:
+        return None
+    if not (parser.outercutoff >= ALL_PAIRS_CUTOFF) or not species.is_cuda:
+        return None
+    key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method, id(packpar))
+    for k, prep in enumerate(_PREP_CACHE):
+        if prep.key == key:
+            if k:
+                _PREP_CACHE.insert(0, _PREP_CACHE.pop(k))
+            return prep
+    prep = Prepared(const, parser, packpar, species, coordinates, method)
+    _PREP_CACHE.insert(0, prep)
+    del _PREP_CACHE[_PREP_CACHE_SIZE:]
+    return prep

@@ -55,6 +55,8 @@ def lib():
         L.seqm_eigh_max_m.restype = ctypes.c_int
         L.seqm_eigh_force_block.argtypes = [ctypes.c_int]
         L.seqm_eigh_force_block.restype = None
+        L.seqm_eigh_tolerance.argtypes = [ctypes.c_double]
+        L.seqm_eigh_tolerance.restype = None
         L.seqm_sp2_workspace.restype = ctypes.c_size_t
         L.seqm_sp2_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64]
         L.seqm_scf_workspace.restype = ctypes.c_size_t
@@ -72,18 +74,22 @@ def lib():
                               [ctypes.POINTER(ctypes.c_int32), VP]
         L.seqm_pair_grad.argtypes = [TP, VP, VP, VP, ci] + [VP] * 7
         L.seqm_dgemm_batched.argtypes = [i64, i64, VP, VP, VP, i64, i64, VP, VP]
+        L.seqm_pair_geometry.argtypes = [TP, VP, cd, VP, VP, VP]
+        L.seqm_pair_geometry_grad.argtypes = [TP, VP, VP, VP, VP, cd, VP, VP]
         for name in EXPORTS:
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
-                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block'):
+                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance'):
                 fn.restype = ctypes.c_int
+        if os.environ.get('SEQM_EIGH_TOL'):
+            L.seqm_eigh_tolerance(float(os.environ['SEQM_EIGH_TOL']))
         _lib = L
     return _lib
 
 
 EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
-           'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_density', 'seqm_sp2_workspace',
-           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched']
+           'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
+           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad']
 
 
 def check(rc, what):

@@ -143,12 +143,12 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv):
     nc = torch.ones(B, dtype=torch.uint8, device=dev)
     nit = torch.zeros(B, dtype=torch.int32, device=dev)
     work = torch.empty(lib().seqm_scf_workspace(B, S, ctypes.byref(opt)), dtype=torch.uint8, device=dev)
-    iters = ctypes.c_int32(0)
+    iters = (ctypes.c_int32 * 2)(0, 0)
     g = [_f64(x) for x in par5]
     check(lib().seqm_scf(topo.ref(), w.c, _p(_f64(M)), *[_p(x) for x in g], _p(topo.nheavy), _p(topo.nhydro),
                          _p(topo.nocc), int(topo.mmax), ctypes.byref(opt), _p(P), _p(F), _p(E), _p(nc), _p(nit),
-                         _p(pv), _p(work), ctypes.byref(iters), _stream()), 'seqm_scf')
-    return P, F, E, nc.bool(), nit, iters.value
+                         _p(pv), _p(work), iters, _stream()), 'seqm_scf')
+    return P, F, E, nc.bool(), nit, (int(iters[0]), int(iters[1]))
 
 
 def pair_grad(topo, atompar, xij, rij, method, P, D, gE, gNuc):
@@ -161,6 +161,30 @@ def pair_grad(topo, atompar, xij, rij, method, P, D, gE, gNuc):
     check(lib().seqm_pair_grad(topo.ref(), _p(atompar), _p(xij), _p(rij), N_GAUSS[method], _p(P), _p(Dc), _p(gE),
                                _p(gNuc), _p(gx), _p(gr), _stream()), 'seqm_pair_grad')
     return gx, gr
+
+
+class PairGeometry(torch.autograd.Function):
+    """coordinates[B,S,3] -> (xij[P,3], rij[P]): the Parser's geometry (reference basics.py:91-108) as one
+    kernel, with the per-atom fixed-order adjoint kernel as backward."""
+
+    @staticmethod
+    def forward(ctx, coordinates, topo, lcf):
+        R = _f64(coordinates)
+        xij = torch.empty(topo.npairs, 3, dtype=torch.float64, device=R.device)
+        rij = torch.empty(topo.npairs, dtype=torch.float64, device=R.device)
+        check(lib().seqm_pair_geometry(topo.ref(), _p(R), float(lcf), _p(xij), _p(rij), _stream()), 'seqm_pair_geometry')
+        ctx.topo, ctx.lcf, ctx.shape = topo, float(lcf), coordinates.shape
+        ctx.save_for_backward(xij, rij)
+        return xij, rij
+
+    @staticmethod
+    def backward(ctx, gx, gr):
+        xij, rij = ctx.saved_tensors
+        gR = torch.zeros(ctx.shape, dtype=torch.float64, device=xij.device)
+        gx, gr = _f64(gx), _f64(gr)
+        check(lib().seqm_pair_geometry_grad(ctx.topo.ref(), _p(xij), _p(rij), _p(gx), _p(gr), ctx.lcf, _p(gR), _stream()),
+              'seqm_pair_geometry_grad')
+        return gR, None, None
 
 
 class PairEnergy(torch.autograd.Function):

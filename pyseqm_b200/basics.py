@@ -117,6 +117,14 @@ class Hamiltonian(torch.nn.Module):
                                                    requires_grad=False)
         if self.scf_backward != 0:
             raise NotImplementedError("scf_backward=1/2 is outside the B200 hot path (see DESIGN.md)")
+        self._eps_cache = None
+
+    def eps_host(self):
+        """scf_eps as a python float, read back from the (possibly device-resident) parameter once"""
+        key = (self.eps.data_ptr(), self.eps._version)
+        if self._eps_cache is None or self._eps_cache[0] != key:
+            self._eps_cache = (key, float(self.eps))
+        return self._eps_cache[1]
 
     def forward(self, const, molsize, nHeavy, nHydro, nocc, Z, maskd, mask, atom_molid, pair_molid, idxi, idxj, ni,
                 nj, xij, rij, parameters, P0=None):
@@ -147,19 +155,35 @@ class Energy(torch.nn.Module):
 
     def forward(self, const, coordinates, species, learned_parameters=dict(), all_terms=False, P0=None, step=0,
                 *args, **kwargs):
-        nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
-            self.parser(const, species, coordinates, *args, **kwargs)
-        if callable(learned_parameters):
-            parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
-        else:
-            parameters = self.packpar(Z, learned_params=learned_parameters)
-        for k, v in parameters.items():
-            if torch.is_tensor(v) and v.requires_grad:
-                raise NotImplementedError("gradients with respect to parameter '%s' are outside the B200 hot path" % k)
+        prep = _engine.prepared_for(const, self.parser, self.packpar, species, coordinates, self.method,
+                                    learned_parameters, kwargs)
         H = self.hamiltonian
-        st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
-                           self.method, run_scf=True, P0=P0, eps=float(H.eps), sp2=H.sp2,
-                           scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER, debug=_scf_loop_mod.debug)
+        if prep is not None:
+            # species-only data cached; only the pair geometry depends on the coordinates
+            nmol, molsize, nHeavy, nHydro, nocc, Z, maskd = prep.nmol, prep.molsize, prep.nHeavy, prep.nHydro, \
+                prep.nocc, prep.Z, prep.maskd
+            atom_molid, pair_molid, idxi, idxj, parameters = prep.atom_molid, prep.pair_molid, prep.idxi, prep.idxj, \
+                prep.parameters
+            xij, rij = _ops.PairGeometry.apply(coordinates, prep.topo, prep.lcf)
+            st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
+                               self.method, run_scf=True, P0=P0, eps=H.eps_host(), sp2=H.sp2,
+                               scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER,
+                               debug=_scf_loop_mod.debug, topo=prep.topo, atompar=prep.atompar, P_guess=prep.P_guess)
+        else:
+            nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
+                self.parser(const, species, coordinates, *args, **kwargs)
+            if callable(learned_parameters):
+                parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
+            else:
+                parameters = self.packpar(Z, learned_params=learned_parameters)
+            for k, v in parameters.items():
+                if torch.is_tensor(v) and v.requires_grad:
+                    raise NotImplementedError("gradients with respect to parameter '%s' are outside the B200 hot path"
+                                              % k)
+            st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
+                               self.method, run_scf=True, P0=P0, eps=H.eps_host(), sp2=H.sp2,
+                               scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER,
+                               debug=_scf_loop_mod.debug)
         P, notconverged = st['P'], st['notconverged']
         Eelec, EnucAB = _ops.PairEnergy.apply(xij, rij, st)
         e = charge = None
@@ -171,9 +195,9 @@ class Energy(torch.nn.Module):
         self.last_state = st
         if all_terms:
             Etot, Enuc = total_energy(nmol, pair_molid, EnucAB, Eelec)
-            Eiso = elec_energy_isolated_atom(const, Z, uss=parameters['U_ss'], upp=parameters['U_pp'],
-                                             gss=parameters['g_ss'], gpp=parameters['g_pp'], gsp=parameters['g_sp'],
-                                             gp2=parameters['g_p2'], hsp=parameters['h_sp'])
+            Eiso = prep.Eiso if prep is not None else elec_energy_isolated_atom(
+                const, Z, uss=parameters['U_ss'], upp=parameters['U_pp'], gss=parameters['g_ss'],
+                gpp=parameters['g_pp'], gsp=parameters['g_sp'], gp2=parameters['g_p2'], hsp=parameters['h_sp'])
             Hf, Eiso_sum = heat_formation(const, nmol, atom_molid, Z, Etot, Eiso, flag=self.Hf_flag)
             return Hf, Etot, Eelec, Enuc, Eiso_sum, EnucAB, e, P, charge, notconverged
         return Eelec, EnucAB, P, notconverged

@@ -37,7 +37,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
                     const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
                     const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
                     double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore,
-                    int warm) {
+                    int warm, double tol) {
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const int nh4 = 4 * nheavy[mol];
@@ -107,7 +107,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
     off = block_sum(off, red);
     tot = block_sum(tot, red);
     if (off == 0.0 || last) break;
-    if (off <= 1.0e-28 * tot) last = true;      // one more sweep after reaching 1e-14 relative
+    if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
     for (int r = 0; r < mp - 1; ++r) {
       if (tid < half) {
         int p, q;
@@ -202,6 +202,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
   }
 }
 
+double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {
@@ -216,14 +217,14 @@ size_t eigh_vstore_doubles(int64_t nmol, int mmax) {
 template <int NT, int MINB>
 static int launch_cfg(int64_t nmol, size_t smem, cudaStream_t st, int S, int mp, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
-                      double* v_out, int32_t* info, double* Vstore, int warm) {
+                      double* v_out, int32_t* info, double* Vstore, int warm, double tol) {
   static thread_local size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
     SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   eigh_density_kernel<NT, MINB><<<(unsigned)nmol, NT, smem, st>>>(S, mp, F, nheavy, nhydro, nocc, active, P, e_out,
-                                                                  v_out, info, Vstore, warm);
+                                                                  v_out, info, Vstore, warm, tol);
   SEQM_CHECK_LAUNCH("eigh_density_kernel");
   return SEQM_OK;
 }
@@ -242,13 +243,13 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   prof_mark("eigh_density", st);
   int rc;
   if (mp <= 32 && !g_force_block_jacobi)
-    rc = launch_eigh_warp(nmol, molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, st);
+    rc = launch_eigh_warp(nmol, molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol, st);
   else if (mp <= 32)
-    rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
+    rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else if (mp <= 64)
-    rc = launch_cfg<512, 2>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
+    rc = launch_cfg<512, 2>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else
-    rc = launch_cfg<1024, 1>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm);
+    rc = launch_cfg<1024, 1>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   prof_mark("end", st);
   return rc;
 }
@@ -261,6 +262,8 @@ extern "C" {
 
 int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
 void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
+
+void seqm_eigh_tolerance(double tol) { g_eigh_tol = tol > 0.0 ? tol : 1.0e-24; }
 
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,

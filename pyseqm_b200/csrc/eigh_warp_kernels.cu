@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(32)
 eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                  const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
                  const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
-                 double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm) {
+                 double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm,
+                 double tol) {
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const int nh4 = 4 * nheavy[mol];
@@ -107,7 +108,7 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
     off = warp_sum(off);
     tot = warp_sum(tot);
     if (off == 0.0 || last) break;
-    if (off <= 1.0e-28 * tot) last = true;
+    if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
     for (int r = 0; r < WN - 1; ++r) {
       // rotation of this lane's pair (computed on the even lane, shared with the odd one)
       double x = 0.0, y = 0.0;
@@ -117,8 +118,15 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
       const double yo = __shfl_xor_sync(FULL, y, 1);
       double c = 1.0, s = 0.0;
       if (!(lane & 1) && y != 0.0) {
-        const double d = yo - x, b = 2.0 * y;          // aqq - app, 2 apq
-        const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) / (fabs(d) + sqrt(d * d + b * b));
+        // t = sgn(theta)/(|theta| + sqrt(theta^2+1)) with theta = (aqq-app)/(2 apq), written without IEEE
+        // division/sqrt: the rotation only has to be orthogonal to rounding (c^2 + s^2 = 1 from one rsqrt)
+        const double d = yo - x, b = 2.0 * y;
+        const double h2 = d * d + b * b;
+        const double hy = h2 * rsqrt(h2);              // sqrt(d^2 + b^2)
+        const double den = fabs(d) + hy;
+        double inv = rsqrt(den * den);                 // 1/den
+        inv = inv * (2.0 - den * inv);                 // one Newton step
+        const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) * inv;
         c = rsqrt(tt * tt + 1.0);
         s = tt * c;
       }
@@ -207,9 +215,9 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
 
 int launch_eigh_warp(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy, const int32_t* nhydro,
                      const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out,
-                     int32_t* info, double* Vstore, int warm, cudaStream_t st) {
+                     int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
   eigh_warp_kernel<<<(unsigned)nmol, 32, 0, st>>>((int)molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info,
-                                                Vstore, warm);
+                                                Vstore, warm, tol);
   SEQM_CHECK_LAUNCH("eigh_warp_kernel");
   return SEQM_OK;
 }

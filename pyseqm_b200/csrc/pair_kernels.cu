@@ -380,6 +380,67 @@ pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double
   gr[p] = ge * eel.d[3] + gn * en.d[3];
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Pair geometry on the device (the arithmetic of the reference Parser, basics.py:91-108) and its adjoint:
+//   d = R_j - R_i, dist = sqrt(d.d) (1e-4 A^2 if zero), xij = d/dist, rij = dist * lcf
+//   grad R[atom] = sum over its pairs of +-( (g_x - (g_x . x) x)/dist + g_r lcf x ), fixed order, no atomics
+// ---------------------------------------------------------------------------------------------
+__global__ void pair_geometry_kernel(seqm_topology_t t, const double* __restrict__ R, double lcf,
+                                     double* __restrict__ xij, double* __restrict__ rij) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= t.npairs) return;
+  const int i = t.idxi[p], j = t.idxj[p];
+  const int S = (int)t.molsize;
+  const double* ri = R + ((size_t)t.atom_mol[i] * S + t.atom_slot[i]) * 3;
+  const double* rj = R + ((size_t)t.atom_mol[j] * S + t.atom_slot[j]) * 3;
+  const double dx = rj[0] - ri[0], dy = rj[1] - ri[1], dz = rj[2] - ri[2];
+  double d2 = dx * dx + dy * dy + dz * dz;
+  if (d2 == 0.0) d2 = 1.0e-4;
+  const double dist = sqrt(d2);
+  xij[3 * p] = dx / dist; xij[3 * p + 1] = dy / dist; xij[3 * p + 2] = dz / dist;
+  rij[p] = dist * lcf;
+}
+
+__device__ __forceinline__ void pair_geom_grad_one(const double* __restrict__ xij, const double* __restrict__ rij,
+                                                   const double* __restrict__ gx, const double* __restrict__ gr,
+                                                   double lcf, int p, double* g) {
+  const double x0 = xij[3 * p], x1 = xij[3 * p + 1], x2 = xij[3 * p + 2];
+  const double g0 = gx[3 * p], g1 = gx[3 * p + 1], g2 = gx[3 * p + 2];
+  const double inv = lcf / rij[p];                  // 1/dist
+  const double dot = g0 * x0 + g1 * x1 + g2 * x2;
+  const double gd = gr[p] * lcf;
+  g[0] = (g0 - dot * x0) * inv + gd * x0;
+  g[1] = (g1 - dot * x1) * inv + gd * x1;
+  g[2] = (g2 - dot * x2) * inv + gd * x2;
+}
+
+__global__ void __launch_bounds__(256)
+pair_geometry_grad_kernel(seqm_topology_t t, const double* __restrict__ xij, const double* __restrict__ rij,
+                          const double* __restrict__ gx, const double* __restrict__ gr, double lcf,
+                          double* __restrict__ gR) {
+  const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (a >= t.natoms) return;
+  double acc[3] = {0.0, 0.0, 0.0}, g[3];
+  for (int q = t.start_i[a] + lane; q < t.start_i[a + 1]; q += 32) {      // atom is i: d = R_j - R_i
+    pair_geom_grad_one(xij, rij, gx, gr, lcf, q, g);
+    acc[0] -= g[0]; acc[1] -= g[1]; acc[2] -= g[2];
+  }
+  for (int q = t.start_j[a] + lane; q < t.start_j[a + 1]; q += 32) {
+    pair_geom_grad_one(xij, rij, gx, gr, lcf, t.perm_j[q], g);
+    acc[0] += g[0]; acc[1] += g[1]; acc[2] += g[2];
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+  if (lane == 0) {
+    double* out = gR + ((size_t)t.atom_mol[a] * t.molsize + t.atom_slot[a]) * 3;
+    out[0] = acc[0]; out[1] = acc[1]; out[2] = acc[2];
+  }
+}
+
 }  // namespace seqm
 
 using namespace seqm;
@@ -498,6 +559,29 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
     SEQM_CHECK_LAUNCH("pair_grad_kernel<HH>");
   }
   prof_mark("end", st);
+  return SEQM_OK;
+}
+
+int seqm_pair_geometry(const seqm_topology_t* topo, const double* R, double lcf, double* xij, double* rij,
+                       void* stream) {
+  SEQM_REQUIRE(topo && R && xij && rij, "seqm_pair_geometry: null pointer");
+  if (topo->npairs == 0) return SEQM_OK;
+  prof_mark("pair_geometry", (cudaStream_t)stream);
+  pair_geometry_kernel<<<cdiv(topo->npairs, 256), 256, 0, (cudaStream_t)stream>>>(*topo, R, lcf, xij, rij);
+  SEQM_CHECK_LAUNCH("pair_geometry_kernel");
+  prof_mark("end", (cudaStream_t)stream);
+  return SEQM_OK;
+}
+
+int seqm_pair_geometry_grad(const seqm_topology_t* topo, const double* xij, const double* rij, const double* gx,
+                            const double* gr, double lcf, double* gR, void* stream) {
+  SEQM_REQUIRE(topo && xij && rij && gx && gr && gR, "seqm_pair_geometry_grad: null pointer");
+  if (topo->natoms == 0) return SEQM_OK;
+  prof_mark("pair_geometry_grad", (cudaStream_t)stream);
+  pair_geometry_grad_kernel<<<cdiv(topo->natoms * 32, 256), 256, 0, (cudaStream_t)stream>>>(*topo, xij, rij, gx, gr,
+                                                                                          lcf, gR);
+  SEQM_CHECK_LAUNCH("pair_geometry_grad_kernel");
+  prof_mark("end", (cudaStream_t)stream);
   return SEQM_OK;
 }
 

@@ -359,7 +359,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   }
   prof_mark("end", st);
   cudaFreeHost(hstat);
-  if (iterations_out) *iterations_out = k;
+  if (iterations_out) { iterations_out[0] = k; iterations_out[1] = (int32_t)left; }
   return SEQM_OK;
 }
 

@@ -187,3 +187,59 @@ def test_force_end_to_end(name):
     assert np.array_equal(notconv.cpu().numpy(), g['notconverged'])
     assert d(P, 'P') < 1e-7, d(P, 'P')
     assert d(force, 'force') < 1e-5, d(force, 'force')
+
+
+@pytest.mark.parametrize('name', ['mixed12_MNDO_eigh_c2', 'small_PM3_eigh_c2'])
+def test_pair_geometry_op_matches_parser(name):
+    """device pair geometry + its adjoint kernel vs the torch Parser and torch autograd"""
+    from pyseqm_b200 import _engine, _ops
+    from pyseqm_b200.basics import Pack_Parameters, Parser
+    from pyseqm_b200.seqm_functions.constants import Constants
+    if name not in golden_names():
+        name = golden_names()[0]
+    dev = _dev()
+    g = _load(name)
+    sp = _params(g)
+    const = Constants().to(dev)
+    species, coords = _t(g['species'], dev), _t(g['coords'], dev)
+    parser = Parser(sp)
+    prep = _engine.Prepared(const, parser, Pack_Parameters(sp).to(dev), species, coords, sp['method'])
+    c1 = coords.clone().requires_grad_(True)
+    out = parser(const, species, c1)
+    xr, rr = out[14], out[15]
+    c2 = coords.clone().requires_grad_(True)
+    xk, rk = _ops.PairGeometry.apply(c2, prep.topo, prep.lcf)
+    assert torch.equal(out[12], prep.idxi) and torch.equal(out[13], prep.idxj)
+    assert float((xk - xr).detach().abs().max()) < 1e-15
+    assert float(((rk - rr) / rr).detach().abs().max()) < 1e-15
+    gen = torch.Generator(device='cpu').manual_seed(5)
+    wx = torch.randn(xr.shape, generator=gen, dtype=torch.float64).to(dev)
+    wr = torch.randn(rr.shape, generator=gen, dtype=torch.float64).to(dev)
+    ((xr * wx).sum() + (rr * wr).sum()).backward()
+    ((xk * wx).sum() + (rk * wr).sum()).backward()
+    scale = float(c1.grad.abs().max())
+    assert float((c1.grad - c2.grad).abs().max()) < 1e-13 * max(scale, 1.0)
+
+
+def test_prepared_path_matches_parser_path():
+    """Energy's species-cached path (infinite cutoff) and the general Parser path (finite cutoff that still keeps
+    every pair) give the same forces and energies"""
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.seqm_functions.constants import Constants
+    dev = _dev()
+    g = _load('small_PM3_eigh_c2')
+    sp = _params(g)
+    const = Constants().to(dev)
+    species = _t(g['species'], dev)
+    res = []
+    for cutoff in (1.0e10, 1.0e4):
+        sp2 = dict(sp, pair_outer_cutoff=cutoff)
+        out = Force(sp2).to(dev)(const, _t(g['coords'], dev).clone(), species)
+        res.append(out)
+    for k in (0, 2, 3, 4):          # force, Etot, Hf, Eelec
+        assert float((res[0][k] - res[1][k]).abs().max()) < 1e-9
+    # second call through the cache (same species tensor) gives identical numbers
+    f = Force(dict(sp, pair_outer_cutoff=1.0e10)).to(dev)
+    a = f(const, _t(g['coords'], dev).clone(), species)
+    b = f(const, _t(g['coords'], dev).clone(), species)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2])
