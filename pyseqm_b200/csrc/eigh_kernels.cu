@@ -243,7 +243,7 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   prof_mark("eigh_density", st);
   int rc;
   if (mp <= 32 && !g_force_block_jacobi)
-    rc = launch_eigh_warp(nmol, molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol, st);
+    rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol, st);
   else if (mp <= 32)
     rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else if (mp <= 64)

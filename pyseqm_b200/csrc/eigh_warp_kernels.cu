@@ -1,23 +1,21 @@
-// K3a for small molecules (packed size m <= 32): one WARP per molecule, the whole matrix in registers.
-// Lane i holds row i of A and row i of the eigenvector matrix V (2 x 32 doubles).  Brent-Luk systolic
-// ordering: rotations always act on the adjacent position pairs (2k, 2k+1), so column indices are compile-time
-// register indices, and after every round rows and columns are physically permuted (rows by a warp shuffle,
-// columns by register renaming) so that all pairs meet in N-1 rounds.  No shared-memory round trips and no
-// block barriers inside a sweep; shared memory is only a staging buffer for the load, the warm-start
-// transform A <- V0^T A V0 and the density product.
+// K3a for small molecules (packed size m <= 32): one WARP per molecule.
+// Lane i owns row i of A and row i of the eigenvector matrix V in registers (2 x N doubles).  Rows never move
+// between lanes; COLUMNS move between register positions.  Ordering: odd-even transposition -- round A pairs
+// the positions (0,1),(2,3),..., round B pairs (1,2),(3,4),...; every rotation also swaps its two columns,
+// which costs nothing because the rotated values are written to the exchanged registers.  After N rounds the
+// column order is reversed and every pair of columns has met exactly once (one sweep); all register indices
+// are compile-time constants.  The row half of the similarity transform needs the partner row: rows are
+// published in shared memory once per round (double buffered) and read back with 128-bit loads; the N/2
+// (c,s) pairs of a round travel through shared memory as well.  Per round and lane: 6N FP64 operations,
+// ~1.5N + 4 shared-memory instructions, two warp shuffles (position bookkeeping), two __syncwarp.
 // reference: seqm/seqm_functions/diag.py:102-172 (sym_eig_trunc), pack.py:7-41
 #include "abi_common.cuh"
 
 namespace seqm {
 
-constexpr int WN = 32;                 // matrix dimension handled per warp
-constexpr int WLD = WN + 1;            // padded smem row
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int WARP_MAX_SWEEPS = 40;
-
-__host__ __device__ constexpr int bl_src(int j) {
-  return j == 0 ? 0 : (j == 2 ? 1 : ((j & 1) == 0 ? j - 2 : (j == WN - 1 ? WN - 2 : j + 2)));
-}
+constexpr int WV_LD = 32;              // row stride of the eigenvector store kept between SCF iterations
 
 __device__ __forceinline__ int pk2pd(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
 
@@ -27,12 +25,91 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// row stride (doubles) of the shared row buffers: even (128-bit access) and 2*LD = 4 (mod 32) words so that
+// the eight lanes of a quarter warp hit disjoint banks when they read eight consecutive rows
+template <int N> struct WarpLd { static constexpr int value = (N <= 18) ? 18 : 34; };
+
+// position paired with position x in a round of parity PAR (x itself when idle)
+template <int N, int PAR> __device__ __forceinline__ int mate_of(int x) {
+  if (x >= N) return x;
+  if (PAR == 0) return x ^ 1;
+  return (x == 0 || x == N - 1) ? x : ((x & 1) ? x + 1 : x - 1);
+}
+
+// one round; Sr = row buffer holding the current A, Sw = buffer that receives the updated rows
+template <int N, int PAR>
+__device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], const double* __restrict__ Sr,
+                                             double* __restrict__ Sw, double* __restrict__ CS, int lane, int rowoff,
+                                             bool on, int& mypos, int& colid) {
+  constexpr int LD = WarpLd<N>::value;
+  constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
+  const int mp = mate_of<N, PAR>(mypos);
+  const bool act = mp != mypos;
+  const bool left = mypos < mp;
+  const int L = on ? (left ? mypos : mp) : 0;               // left position of my pair (own position when idle)
+  const int partner = __shfl_sync(FULL, colid, mp & 31);    // row that owns the column at the mate position
+  const int prow = partner * LD;
+  double c = 1.0, s = 0.0;
+  {
+    const double x0 = Sr[rowoff + L], x1 = Sr[rowoff + L + 1];
+    const double y0 = Sr[prow + L], y1 = Sr[prow + L + 1];
+    const double app = left ? x0 : y0, apq = left ? x1 : y1, aqq = left ? y1 : x1;
+    if (act && apq != 0.0) {
+      // t = sgn(theta)/(|theta| + sqrt(theta^2+1)), theta = (aqq-app)/(2 apq), without IEEE division/sqrt: the
+      // rotation only has to be orthogonal to rounding (c^2 + s^2 = 1 comes from one rsqrt)
+      const double d = aqq - app, b = 2.0 * apq;
+      const double h2 = d * d + b * b;
+      const double hy = h2 * rsqrt(h2);
+      const double den = fabs(d) + hy;
+      double inv = rsqrt(den * den);
+      inv = inv * (2.0 - den * inv);
+      const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) * inv;
+      c = rsqrt(tt * tt + 1.0);
+      s = tt * c;
+    }
+    if (act && left) *reinterpret_cast<double2*>(&CS[2 * (L >> 1)]) = make_double2(c, s);
+  }
+  __syncwarp();
+  // rows: A <- J^T A   (row p: c*row_p - s*row_q, row q: s*row_p + c*row_q)
+  {
+    const double sg = act ? (left ? -s : s) : 0.0;
+#pragma unroll
+    for (int jj = 0; jj < N / 2; ++jj) {
+      const double2 b = *reinterpret_cast<const double2*>(&Sr[prow + 2 * jj]);
+      a[2 * jj] = c * a[2 * jj] + sg * b.x;
+      a[2 * jj + 1] = c * a[2 * jj + 1] + sg * b.y;
+    }
+  }
+  // columns: A <- A J, V <- V J, and the two columns of every pair change places
+#pragma unroll
+  for (int k = 0; k < NPAIR; ++k) {
+    const double2 cs = *reinterpret_cast<const double2*>(&CS[2 * k]);
+    const int j0 = 2 * k + PAR, j1 = j0 + 1;
+    const double a0 = a[j0], a1 = a[j1];
+    a[j1] = cs.x * a0 - cs.y * a1;
+    a[j0] = cs.y * a0 + cs.x * a1;
+    const double v0 = v[j0], v1 = v[j1];
+    v[j1] = cs.x * v0 - cs.y * v1;
+    v[j0] = cs.y * v0 + cs.x * v1;
+  }
+  if (on) {
+#pragma unroll
+    for (int jj = 0; jj < N / 2; ++jj)
+      *reinterpret_cast<double2*>(&Sw[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
+  }
+  colid = __shfl_sync(FULL, colid, mate_of<N, PAR>(lane) & 31);
+  mypos = mp;
+  __syncwarp();
+}
+
+template <int N>
 __global__ void __launch_bounds__(32)
 eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                  const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
                  const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
                  double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm,
                  double tol) {
+  constexpr int LD = WarpLd<N>::value;
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const int nh4 = 4 * nheavy[mol];
@@ -41,144 +118,131 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   const int n4 = 4 * S;
   const size_t base = (size_t)mol * n4 * n4;
   const int lane = threadIdx.x;
-  __shared__ double S0[WN * WLD];
-  __shared__ double S1[WN * WLD];
-  double a[WN], v[WN];
+  const bool on = lane < N;
+  const int rowoff = (on ? lane : 0) * LD;
+  __shared__ __align__(16) double S0[N * LD];
+  __shared__ __align__(16) double S1[N * LD];
+  __shared__ __align__(16) double CS[N];
+  double a[N], v[N];
 
-  // ---- load the packed matrix (upper triangle, like eigh(UPLO='U')): coalesced rows through shared memory
-  for (int r = 0; r < WN; ++r) {
+  // ---- load the packed matrix (upper triangle, like eigh(UPLO='U')) through shared memory
+  for (int r = 0; r < N; ++r) {
     double x = 0.0;
     if (r < m && lane < m) {
       const int rr = r <= lane ? r : lane, cc = r <= lane ? lane : r;
       x = F[base + (size_t)pk2pd(rr, nh4) * n4 + pk2pd(cc, nh4)];
     }
-    S0[r * WLD + lane] = x;
+    if (on) S0[r * LD + lane] = x;
   }
   __syncwarp();
 #pragma unroll
-  for (int j = 0; j < WN; ++j) a[j] = S0[lane * WLD + j];
+  for (int jj = 0; jj < N / 2; ++jj) {
+    const double2 t = *reinterpret_cast<const double2*>(&S0[rowoff + 2 * jj]);
+    a[2 * jj] = on ? t.x : 0.0;
+    a[2 * jj + 1] = on ? t.y : 0.0;
+  }
   __syncwarp();
-  double* Vg = Vstore ? Vstore + (size_t)mol * WN * WN : nullptr;
+  double* Vg = Vstore ? Vstore + (size_t)mol * WV_LD * WV_LD : nullptr;
   if (warm && Vg) {
-    // V0 -> S0 (coalesced), own row to registers
-    for (int r = 0; r < WN; ++r) S0[r * WLD + lane] = Vg[r * WN + lane];
+    // V0 -> S1 (coalesced), own row to registers
+    for (int r = 0; r < N; ++r)
+      if (on) S1[r * LD + lane] = Vg[r * WV_LD + lane];
     __syncwarp();
 #pragma unroll
-    for (int j = 0; j < WN; ++j) v[j] = S0[lane * WLD + j];
+    for (int jj = 0; jj < N / 2; ++jj) {
+      const double2 t = *reinterpret_cast<const double2*>(&S1[rowoff + 2 * jj]);
+      v[2 * jj] = on ? t.x : 0.0;
+      v[2 * jj + 1] = on ? t.y : 0.0;
+    }
     // T = A V0 : row `lane`
-    double t[WN];
+    double t[N];
 #pragma unroll
-    for (int j = 0; j < WN; ++j) t[j] = 0.0;
+    for (int j = 0; j < N; ++j) t[j] = 0.0;
 #pragma unroll
-    for (int k = 0; k < WN; ++k) {
+    for (int k = 0; k < N; ++k) {
       const double ak = a[k];
 #pragma unroll
-      for (int j = 0; j < WN; ++j) t[j] = fma(ak, S0[k * WLD + j], t[j]);
+      for (int jj = 0; jj < N / 2; ++jj) {
+        const double2 w = *reinterpret_cast<const double2*>(&S1[k * LD + 2 * jj]);
+        t[2 * jj] = fma(ak, w.x, t[2 * jj]);
+        t[2 * jj + 1] = fma(ak, w.y, t[2 * jj + 1]);
+      }
     }
+    if (on) {
 #pragma unroll
-    for (int j = 0; j < WN; ++j) S1[lane * WLD + j] = t[j];
+      for (int jj = 0; jj < N / 2; ++jj)
+        *reinterpret_cast<double2*>(&S0[rowoff + 2 * jj]) = make_double2(t[2 * jj], t[2 * jj + 1]);
+    }
     __syncwarp();
     // A = V0^T T : row `lane` = sum_k V0[k][lane] T[k][:]
 #pragma unroll
-    for (int j = 0; j < WN; ++j) a[j] = 0.0;
-    for (int k = 0; k < WN; ++k) {
-      const double vk = S0[k * WLD + lane];
+    for (int j = 0; j < N; ++j) a[j] = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < N; ++k) {
+      const double vk = on ? S1[k * LD + lane] : 0.0;
 #pragma unroll
-      for (int j = 0; j < WN; ++j) a[j] = fma(vk, S1[k * WLD + j], a[j]);
+      for (int jj = 0; jj < N / 2; ++jj) {
+        const double2 w = *reinterpret_cast<const double2*>(&S0[k * LD + 2 * jj]);
+        a[2 * jj] = fma(vk, w.x, a[2 * jj]);
+        a[2 * jj + 1] = fma(vk, w.y, a[2 * jj + 1]);
+      }
+    }
+    __syncwarp();
+    if (on) {
+#pragma unroll
+      for (int jj = 0; jj < N / 2; ++jj)
+        *reinterpret_cast<double2*>(&S0[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
     }
     __syncwarp();
   } else {
 #pragma unroll
-    for (int j = 0; j < WN; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
+    for (int j = 0; j < N; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
   }
+  // S0 holds the rows of the current A
 
-  // source position of this lane's row after the round's permutation
-  const int q = bl_src(lane);
-  const bool q_even = (q & 1) == 0;
+  int mypos = lane;        // register position of column `lane` (the diagonal element of this row)
+  int colid = on ? lane : 0;   // column that sits at position `lane`
   int sweeps = 0;
   bool last = false;
   for (; sweeps < WARP_MAX_SWEEPS; ++sweeps) {
     double off = 0.0, tot = 0.0;
 #pragma unroll
-    for (int j = 0; j < WN; ++j) {
+    for (int j = 0; j < N; ++j) {
       const double x = a[j] * a[j];
       tot += x;
-      off += (j == lane) ? 0.0 : x;
+      off += (j == mypos) ? 0.0 : x;
     }
     off = warp_sum(off);
     tot = warp_sum(tot);
     if (off == 0.0 || last) break;
     if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
-    for (int r = 0; r < WN - 1; ++r) {
-      // rotation of this lane's pair (computed on the even lane, shared with the odd one)
-      double x = 0.0, y = 0.0;
-#pragma unroll
-      for (int k = 0; k < WN / 2; ++k)
-        if ((lane >> 1) == k) { x = a[2 * k]; y = a[2 * k + 1]; }
-      const double yo = __shfl_xor_sync(FULL, y, 1);
-      double c = 1.0, s = 0.0;
-      if (!(lane & 1) && y != 0.0) {
-        // t = sgn(theta)/(|theta| + sqrt(theta^2+1)) with theta = (aqq-app)/(2 apq), written without IEEE
-        // division/sqrt: the rotation only has to be orthogonal to rounding (c^2 + s^2 = 1 from one rsqrt)
-        const double d = yo - x, b = 2.0 * y;
-        const double h2 = d * d + b * b;
-        const double hy = h2 * rsqrt(h2);              // sqrt(d^2 + b^2)
-        const double den = fabs(d) + hy;
-        double inv = rsqrt(den * den);                 // 1/den
-        inv = inv * (2.0 - den * inv);                 // one Newton step
-        const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) * inv;
-        c = rsqrt(tt * tt + 1.0);
-        s = tt * c;
-      }
-      c = __shfl_sync(FULL, c, lane & ~1);
-      s = __shfl_sync(FULL, s, lane & ~1);
-      // columns: A <- A J, V <- V J
-#pragma unroll
-      for (int k = 0; k < WN / 2; ++k) {
-        const double ck = __shfl_sync(FULL, c, 2 * k), sk = __shfl_sync(FULL, s, 2 * k);
-        const double a0 = a[2 * k], a1 = a[2 * k + 1];
-        a[2 * k] = ck * a0 - sk * a1;
-        a[2 * k + 1] = sk * a0 + ck * a1;
-        const double v0 = v[2 * k], v1 = v[2 * k + 1];
-        v[2 * k] = ck * v0 - sk * v1;
-        v[2 * k + 1] = sk * v0 + ck * v1;
-      }
-      // rows: A <- J^T A, then rows and columns move to their next-round positions
-      const double cq = __shfl_sync(FULL, c, q), sq = __shfl_sync(FULL, s, q);
-      double na[WN], nv[WN];
-#pragma unroll
-      for (int j = 0; j < WN; ++j) {
-        const double bj = a[bl_src(j)];
-        const double xq = __shfl_sync(FULL, bj, q), xp = __shfl_sync(FULL, bj, q ^ 1);
-        na[j] = q_even ? cq * xq - sq * xp : sq * xp + cq * xq;
-        nv[j] = v[bl_src(j)];
-      }
-#pragma unroll
-      for (int j = 0; j < WN; ++j) { a[j] = na[j]; v[j] = nv[j]; }
+    for (int r = 0; r < N; r += 2) {
+      jacobi_round<N, 0>(a, v, S0, S1, CS, lane, rowoff, on, mypos, colid);
+      jacobi_round<N, 1>(a, v, S1, S0, CS, lane, rowoff, on, mypos, colid);
     }
   }
   if (info && lane == 0) info[mol] = sweeps;
   if (Vg) {
 #pragma unroll
-    for (int j = 0; j < WN; ++j) S0[lane * WLD + j] = v[j];
+    for (int jj = 0; jj < N / 2; ++jj)
+      if (on) *reinterpret_cast<double2*>(&S1[rowoff + 2 * jj]) = make_double2(v[2 * jj], v[2 * jj + 1]);
     __syncwarp();
-    for (int r = 0; r < WN; ++r) Vg[r * WN + lane] = S0[r * WLD + lane];
+    for (int r = 0; r < N; ++r)
+      if (on) Vg[r * WV_LD + lane] = S1[r * LD + lane];
     __syncwarp();
   }
 
-  // eigenvalue of position `lane`; positions that belong to the padding (unit vectors on rows >= m)
-  double e = 0.0;
-#pragma unroll
-  for (int j = 0; j < WN; ++j)
-    if (j == lane) e = a[j];
+  // eigenvalue at POSITION `lane`: the diagonal element of the row that owns that column
+  const double e = on ? S0[colid * LD + lane] : 0.0;
+  // positions that belong to the padding carry unit vectors on rows >= m
   unsigned dummy = 0u;
 #pragma unroll
-  for (int p = 0; p < WN; ++p)
-    if (__any_sync(FULL, lane >= m && v[p] != 0.0)) dummy |= 1u << p;
-  const bool real = !((dummy >> lane) & 1u);
+  for (int p = 0; p < N; ++p)
+    if (__any_sync(FULL, on && lane >= m && v[p] != 0.0)) dummy |= 1u << p;
+  const bool real = on && !((dummy >> lane) & 1u);
   int rank = 0;
 #pragma unroll
-  for (int p = 0; p < WN; ++p) {
+  for (int p = 0; p < N; ++p) {
     const double ep = __shfl_sync(FULL, e, p);
     if (!((dummy >> p) & 1u) && (ep < e || (ep == e && p < lane))) ++rank;
   }
@@ -190,36 +254,69 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   }
   if (v_out) {
 #pragma unroll
-    for (int p = 0; p < WN; ++p) {
+    for (int p = 0; p < N; ++p) {
       const int rp = __shfl_sync(FULL, rank, p);
       if (!((dummy >> p) & 1u) && lane < m) v_out[base + (size_t)lane * n4 + rp] = v[p];
     }
   }
   // P = 2 W W^T with W = occupied columns of V
+  __syncwarp();
 #pragma unroll
-  for (int j = 0; j < WN; ++j) {
-    v[j] = ((occmask >> j) & 1u) ? v[j] : 0.0;
-    S0[lane * WLD + j] = v[j];
+  for (int j = 0; j < N; ++j) v[j] = ((occmask >> j) & 1u) ? v[j] : 0.0;
+  if (on) {
+#pragma unroll
+    for (int jj = 0; jj < N / 2; ++jj)
+      *reinterpret_cast<double2*>(&S0[rowoff + 2 * jj]) = make_double2(v[2 * jj], v[2 * jj + 1]);
   }
   __syncwarp();
   for (int i2 = 0; i2 < m; ++i2) {
-    double acc = 0.0;
+    double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
-    for (int j = 0; j < WN; ++j) acc = fma(v[j], S0[i2 * WLD + j], acc);
-    S1[i2 * WLD + lane] = 2.0 * acc;          // P[lane][i2] == P[i2][lane]
+    for (int jj = 0; jj < N / 2; ++jj) {
+      const double2 w = *reinterpret_cast<const double2*>(&S0[i2 * LD + 2 * jj]);
+      acc0 = fma(v[2 * jj], w.x, acc0);
+      acc1 = fma(v[2 * jj + 1], w.y, acc1);
+    }
+    if (on) S1[i2 * LD + lane] = 2.0 * (acc0 + acc1);          // P[lane][i2] == P[i2][lane]
   }
   __syncwarp();
   for (int i2 = 0; i2 < m; ++i2)
-    if (lane < m) P[base + (size_t)pk2pd(i2, nh4) * n4 + pk2pd(lane, nh4)] = S1[i2 * WLD + lane];
+    if (lane < m) P[base + (size_t)pk2pd(i2, nh4) * n4 + pk2pd(lane, nh4)] = S1[i2 * LD + lane];
 }
 
-int launch_eigh_warp(int64_t nmol, int64_t molsize, const double* F, const int32_t* nheavy, const int32_t* nhydro,
-                     const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out,
-                     int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
-  eigh_warp_kernel<<<(unsigned)nmol, 32, 0, st>>>((int)molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info,
-                                                Vstore, warm, tol);
+template <int N>
+static int launch_n(int64_t nmol, int S, const double* F, const int32_t* nheavy, const int32_t* nhydro,
+                    const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out, int32_t* info,
+                    double* Vstore, int warm, double tol, cudaStream_t st) {
+  static thread_local bool configured = false;
+  if (!configured) {
+    SEQM_CUDA(cudaFuncSetAttribute(eigh_warp_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                   (int)cudaSharedmemCarveoutMaxShared));
+    configured = true;
+  }
+  eigh_warp_kernel<N><<<(unsigned)nmol, 32, 0, st>>>(S, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore,
+                                                   warm, tol);
   SEQM_CHECK_LAUNCH("eigh_warp_kernel");
   return SEQM_OK;
+}
+
+// mp = even padded size (<= 32)
+int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, const int32_t* nheavy,
+                     const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
+                     double* v_out, int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
+#define SEQM_WARP_CASE(NN)                                                                                          \
+  if (mp <= NN)                                                                                                     \
+    return launch_n<NN>(nmol, (int)molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, tol, st)
+  SEQM_WARP_CASE(8);
+  SEQM_WARP_CASE(12);
+  SEQM_WARP_CASE(16);
+  SEQM_WARP_CASE(20);
+  SEQM_WARP_CASE(24);
+  SEQM_WARP_CASE(28);
+  SEQM_WARP_CASE(30);
+  SEQM_WARP_CASE(32);
+#undef SEQM_WARP_CASE
+  return fail(SEQM_EUNSUPPORTED, "launch_eigh_warp: packed size above 32");
 }
 
 }  // namespace seqm

@@ -92,6 +92,43 @@ def test_eigh_kernels_random(force_block):
         assert float((C.T @ C - torch.eye(m)).abs().max()) < 1e-13
 
 
+@pytest.mark.parametrize('mmax', [2, 7, 12, 15, 20, 23, 27, 30, 32])
+def test_eigh_warp_kernel_sizes(mmax):
+    """every instantiation of the warp Jacobi kernel (padded sizes 8..32) on batches of mixed sizes <= mmax"""
+    from pyseqm_b200 import _ops
+    import seqm_oracle as orc
+    dev = _dev()
+    rng = np.random.RandomState(100 + mmax)
+    shapes = [(mmax // 4, mmax % 4)]
+    for _ in range(40):
+        m = int(rng.randint(1, mmax + 1))
+        a = int(rng.randint(0, m // 4 + 1))
+        shapes.append((a, m - 4 * a))
+    S = max(a + b for a, b in shapes)
+    n4 = 4 * S
+    nH = torch.tensor([a for a, b in shapes]); nh = torch.tensor([b for a, b in shapes])
+    nocc = torch.tensor([max(1, (4 * a + b) // 2) for a, b in shapes])
+    F = torch.zeros(len(shapes), n4, n4)
+    for b_, (a, h) in enumerate(shapes):
+        m = 4 * a + h
+        X = torch.as_tensor(rng.standard_normal((m, m))); X = X + X.T
+        if b_ % 3 == 0:
+            X = X * 1e-3 + torch.diag(torch.as_tensor(rng.standard_normal(m) * 10.0))     # nearly diagonal
+        Fp = torch.zeros(1, m, m); Fp[0] = X
+        F[b_] = orc.unpack(Fp, nH[b_:b_ + 1], nh[b_:b_ + 1], n4)[0]
+    Pref, eref, _ = orc.density_eigh(F, nH, nh, nocc, want_eig=True)
+    i32 = torch.int32
+    P, e, v = _ops.eigh_density(F.to(dev), nH.to(dev).to(i32), nh.to(dev).to(i32), nocc.to(dev).to(i32), S, mmax,
+                                want_eig=True)
+    assert float((e.cpu() - eref).abs().max()) < 2e-12
+    assert float((P.cpu() - Pref).abs().max()) < 1e-11
+    assert float((P - P.transpose(1, 2)).abs().max()) == 0.0
+    for b_, (a, h) in enumerate(shapes):
+        m = 4 * a + h
+        C = v[b_, :m, :m].cpu()
+        assert float((C.T @ C - torch.eye(m)).abs().max()) < 1e-13
+
+
 @pytest.mark.parametrize('name', golden_names())
 def test_hcore_fock_density_ops(name):
     """op-level parity on the reference's own intermediate tensors"""
@@ -237,7 +274,7 @@ def test_prepared_path_matches_parser_path():
         out = Force(sp2).to(dev)(const, _t(g['coords'], dev).clone(), species)
         res.append(out)
     for k in (0, 2, 3, 4):          # force, Etot, Hf, Eelec
-        assert float((res[0][k] - res[1][k]).abs().max()) < 1e-9
+        assert float((res[0][k] - res[1][k]).detach().abs().max()) < 1e-9
     # second call through the cache (same species tensor) gives identical numbers
     f = Force(dict(sp, pair_outer_cutoff=1.0e10)).to(dev)
     a = f(const, _t(g['coords'], dev).clone(), species)
