@@ -11,6 +11,7 @@ GPU (torchrun), every rank runs its own 1024-molecule shard (weak scaling), no c
 one all_gather of the energies at the end of every step.
 """
 import argparse
+import datetime
 import json
 import os
 import subprocess
@@ -40,20 +41,28 @@ def peaks():
 
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons while the timed region runs: ONE long-running nvidia-smi process
-    (-lms 200) started before the timed region and stopped after it."""
+    (-lms 20, time-stamped rows) started before the warm-up (its start-up takes longer than a short timed region)
+    and stopped after the timed region; only rows stamped inside [mark_begin, mark_end] are summarised."""
 
     def __init__(self, index):
-        self.index, self.proc, self.rows = index, None, []
+        self.index, self.proc, self.rows, self.t0, self.t1 = index, None, [], None, None
 
     def start(self):
-        q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
-            'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+        q = 'timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,' \
+            'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,' \
+            'clocks_event_reasons.sw_power_cap'
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
-                                          '--format=csv,noheader,nounits', '-lms', '200'], stdout=subprocess.PIPE,
+                                          '--format=csv,noheader,nounits', '-lms', '20'], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
+
+    def mark_begin(self):
+        self.t0 = datetime.datetime.now()
+
+    def mark_end(self):
+        self.t1 = datetime.datetime.now()
 
     def stop(self):
         if self.proc is None:
@@ -66,17 +75,26 @@ class ClockSampler:
             out = ''
         for line in out.strip().splitlines():
             t = [x.strip() for x in line.split(',')]
-            if len(t) >= 6:
-                self.rows.append(t)
+            if len(t) >= 7:
+                try:
+                    ts = datetime.datetime.strptime(t[0], '%Y/%m/%d %H:%M:%S.%f')
+                    float(t[1])
+                except ValueError:
+                    continue
+                self.rows.append((ts, t[1:]))
 
     def summary(self):
         if not self.rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(float(r[0]) for r in self.rows)
+        inside = [r for ts, r in self.rows if self.t0 is not None and self.t0 <= ts <= (self.t1 or ts)]
+        window = "timed region"
+        if not inside:      # region shorter than the sampling period: the rows under the same load just before it
+            inside, window = [r for ts, r in self.rows], "warm-up + timed region"
+        sm = sorted(float(r[0]) for r in inside)
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in inside)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(inside[0][1]), "reasons": reasons,
+                "samples": len(inside), "window": window}
 
 
 def run_reference(args, rank, world):
@@ -89,7 +107,7 @@ def run_reference(args, rank, world):
     from pyseqm_b200 import synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    nsample = 128
+    nsample = 512
     sp, xyz = synth.benzene(nsample, seed=0)
     species, coords = torch.as_tensor(sp), torch.as_tensor(xyz)
     times = []
@@ -149,6 +167,7 @@ def run_gpu(args, rank, world, local_rank):
     torch.cuda.set_device(dev)
     if world > 1:
         import torch.distributed as dist
+        from pyseqm_b200.distributed import gather_molecules
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     sp, xyz = synth.benzene(NMOL, seed=rank)
@@ -162,12 +181,10 @@ def run_gpu(args, rank, world, local_rank):
     def flush():
         flush_buf.fill_(1)
 
-    gathered = [torch.empty(NMOL, device=dev) for _ in range(world)] if world > 1 else None
-
     def step(x):
         out = force_mod(const, x, species)
         if world > 1:
-            dist.all_gather(gathered, out[2].detach())
+            gather_molecules(out[2], NMOL * world, world)     # energies of every shard, global molecule order
         return out
 
     def barrier():
@@ -175,14 +192,15 @@ def run_gpu(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for _ in range(args.warmup):
         out = step(coords.clone())
     nconv_fail = int(out[10].sum())
     # ---- resident-input timing ----
-    sampler = ClockSampler(local_rank)
     barrier()
-    if rank == 0:
-        sampler.start()
+    sampler.mark_begin()
     l0 = L.seqm_launch_count()
     evs = []
     for _ in range(args.steps):
@@ -208,6 +226,7 @@ def run_gpu(args, rank, world, local_rank):
         e_host.copy_(o[2].detach(), non_blocking=True)
         torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    sampler.mark_end()
     if rank == 0:
         sampler.stop()
     t = torch.tensor([total_ms, e2e_ms], device=dev)
@@ -261,10 +280,11 @@ def run_gpu(args, rank, world, local_rank):
     import seqm_oracle as orc
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    ns = 128
+    ns, reps = NMOL, 4
     t0 = time.time()
-    orc.run(torch.as_tensor(sp[:ns]), torch.as_tensor(xyz[:ns]), method='AM1', scf_eps=1e-6, converger=(2, 0.0))
-    cpu_s = time.time() - t0
+    for _ in range(reps):
+        orc.run(torch.as_tensor(sp), torch.as_tensor(xyz), method='AM1', scf_eps=1e-6, converger=(2, 0.0))
+    cpu_s = (time.time() - t0) / reps
     ms_step = total_ms / args.steps
     nm_total = NMOL * world
     print(json.dumps({
@@ -280,7 +300,7 @@ def run_gpu(args, rank, world, local_rank):
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
         "profile_one_step": prof,
         "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": "port",
-                         "sample": "first %d of the 1024 benzenes, one Force-equivalent call of the oracle" % ns}}))
+                         "sample": "the %d benzenes of rank 0, %d Force-equivalent calls of the oracle" % (ns, reps)}}))
     if world > 1:
         dist.destroy_process_group()
 

@@ -36,61 +36,74 @@ template <int N, int PAR> __device__ __forceinline__ int mate_of(int x) {
   return (x == 0 || x == N - 1) ? x : ((x & 1) ? x + 1 : x - 1);
 }
 
-// one round; Sr = row buffer holding the current A, Sw = buffer that receives the updated rows
+// V <- V J for a round of parity PAR whose (c,s) pairs are in CSp (the columns of every pair change places)
+template <int N, int PAR>
+__device__ __forceinline__ void v_update(double (&v)[N], const double* __restrict__ CSp) {
+  constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
+#pragma unroll
+  for (int k = 0; k < NPAIR; ++k) {
+    const double2 cs = *reinterpret_cast<const double2*>(&CSp[2 * k]);
+    const int j0 = 2 * k + PAR, j1 = j0 + 1;
+    const double v0 = v[j0], v1 = v[j1];
+    v[j1] = cs.x * v0 - cs.y * v1;
+    v[j0] = cs.y * v0 + cs.x * v1;
+  }
+}
+
+// one round; Sr = row buffer holding the current A, Sw = buffer that receives the updated rows.
+// CS = [2][N]: (c,s) pairs of the last A round and of the last B round.  The eigenvector update of the PREVIOUS
+// round is executed here, next to the (long, dependent) rotation computation, so that the FP64 pipe has
+// independent work while that chain runs.
 template <int N, int PAR>
 __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], const double* __restrict__ Sr,
                                              double* __restrict__ Sw, double* __restrict__ CS, int lane, int rowoff,
                                              bool on, int& mypos, int& colid) {
   constexpr int LD = WarpLd<N>::value;
   constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
+  double* CSc = CS + PAR * N;
+  const double* CSp = CS + (1 - PAR) * N;
   const int mp = mate_of<N, PAR>(mypos);
   const bool act = mp != mypos;
   const bool left = mypos < mp;
   const int L = on ? (left ? mypos : mp) : 0;               // left position of my pair (own position when idle)
   const int partner = __shfl_sync(FULL, colid, mp & 31);    // row that owns the column at the mate position
   const int prow = partner * LD;
-  double c = 1.0, s = 0.0;
-  {
-    const double x0 = Sr[rowoff + L], x1 = Sr[rowoff + L + 1];
-    const double y0 = Sr[prow + L], y1 = Sr[prow + L + 1];
-    const double app = left ? x0 : y0, apq = left ? x1 : y1, aqq = left ? y1 : x1;
-    if (act && apq != 0.0) {
-      // t = sgn(theta)/(|theta| + sqrt(theta^2+1)), theta = (aqq-app)/(2 apq), without IEEE division/sqrt: the
-      // rotation only has to be orthogonal to rounding (c^2 + s^2 = 1 comes from one rsqrt)
-      const double d = aqq - app, b = 2.0 * apq;
-      const double h2 = d * d + b * b;
-      const double hy = h2 * rsqrt(h2);
-      const double den = fabs(d) + hy;
-      double inv = rsqrt(den * den);
-      inv = inv * (2.0 - den * inv);
-      const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) * inv;
-      c = rsqrt(tt * tt + 1.0);
-      s = tt * c;
-    }
-    if (act && left) *reinterpret_cast<double2*>(&CS[2 * (L >> 1)]) = make_double2(c, s);
+  const double x0 = Sr[rowoff + L], x1 = Sr[rowoff + L + 1];
+  const double y0 = Sr[prow + L], y1 = Sr[prow + L + 1];
+  double b[N];
+#pragma unroll
+  for (int jj = 0; jj < N / 2; ++jj) {
+    const double2 t = *reinterpret_cast<const double2*>(&Sr[prow + 2 * jj]);
+    b[2 * jj] = t.x;
+    b[2 * jj + 1] = t.y;
   }
+  v_update<N, 1 - PAR>(v, CSp);
+  // rotation: with r = 1/sqrt(d^2+b^2), u = (1 + |d| r)/2 = cos^2, c = sqrt(u), s = +-|b| r / (2c); branch free,
+  // two rsqrt, and c^2 + s^2 = 1 to rounding whatever the accuracy of r
+  const double app = left ? x0 : y0, apq = left ? x1 : y1, aqq = left ? y1 : x1;
+  const double d = aqq - app, bb = 2.0 * apq;
+  const double h2 = fmax(d * d + bb * bb, 1.0e-300);
+  const double r = rsqrt(h2);
+  const double u = 0.5 + 0.5 * fabs(d) * r;
+  const double w = rsqrt(u);
+  const bool rot = act && apq != 0.0;
+  const double c = rot ? u * w : 1.0;
+  const double sa = 0.5 * fabs(bb) * r * w;
+  const double s = rot ? (((d >= 0.0) == (bb >= 0.0)) ? sa : -sa) : 0.0;
+  if (act && left) *reinterpret_cast<double2*>(&CSc[2 * (L >> 1)]) = make_double2(c, s);
   __syncwarp();
   // rows: A <- J^T A   (row p: c*row_p - s*row_q, row q: s*row_p + c*row_q)
-  {
-    const double sg = act ? (left ? -s : s) : 0.0;
+  const double sg = left ? -s : s;
 #pragma unroll
-    for (int jj = 0; jj < N / 2; ++jj) {
-      const double2 b = *reinterpret_cast<const double2*>(&Sr[prow + 2 * jj]);
-      a[2 * jj] = c * a[2 * jj] + sg * b.x;
-      a[2 * jj + 1] = c * a[2 * jj + 1] + sg * b.y;
-    }
-  }
-  // columns: A <- A J, V <- V J, and the two columns of every pair change places
+  for (int j = 0; j < N; ++j) a[j] = c * a[j] + sg * b[j];
+  // columns: A <- A J with the swap
 #pragma unroll
   for (int k = 0; k < NPAIR; ++k) {
-    const double2 cs = *reinterpret_cast<const double2*>(&CS[2 * k]);
+    const double2 cs = *reinterpret_cast<const double2*>(&CSc[2 * k]);
     const int j0 = 2 * k + PAR, j1 = j0 + 1;
     const double a0 = a[j0], a1 = a[j1];
     a[j1] = cs.x * a0 - cs.y * a1;
     a[j0] = cs.y * a0 + cs.x * a1;
-    const double v0 = v[j0], v1 = v[j1];
-    v[j1] = cs.x * v0 - cs.y * v1;
-    v[j0] = cs.y * v0 + cs.x * v1;
   }
   if (on) {
 #pragma unroll
@@ -100,6 +113,11 @@ __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], con
   colid = __shfl_sync(FULL, colid, mate_of<N, PAR>(lane) & 31);
   mypos = mp;
   __syncwarp();
+}
+
+// column index that the first (fake) pending B-round update maps to position j
+template <int N> __host__ __device__ constexpr int preswap(int j) {
+  return (j == 0 || j >= N - 1) ? j : ((j & 1) ? j + 1 : j - 1);
 }
 
 template <int N>
@@ -122,7 +140,7 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   const int rowoff = (on ? lane : 0) * LD;
   __shared__ __align__(16) double S0[N * LD];
   __shared__ __align__(16) double S1[N * LD];
-  __shared__ __align__(16) double CS[N];
+  __shared__ __align__(16) double CS[2 * N];
   double a[N], v[N];
 
   // ---- load the packed matrix (upper triangle, like eigh(UPLO='U')) through shared memory
@@ -149,11 +167,7 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
       if (on) S1[r * LD + lane] = Vg[r * WV_LD + lane];
     __syncwarp();
 #pragma unroll
-    for (int jj = 0; jj < N / 2; ++jj) {
-      const double2 t = *reinterpret_cast<const double2*>(&S1[rowoff + 2 * jj]);
-      v[2 * jj] = on ? t.x : 0.0;
-      v[2 * jj + 1] = on ? t.y : 0.0;
-    }
+    for (int j = 0; j < N; ++j) v[j] = on ? S1[rowoff + preswap<N>(j)] : 0.0;
     // T = A V0 : row `lane`
     double t[N];
 #pragma unroll
@@ -196,9 +210,12 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
     __syncwarp();
   } else {
 #pragma unroll
-    for (int j = 0; j < N; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
+    for (int j = 0; j < N; ++j) v[j] = (preswap<N>(j) == lane) ? 1.0 : 0.0;
   }
-  // S0 holds the rows of the current A
+  // S0 holds the rows of the current A; v is stored with the column pairs of a B round exchanged and the
+  // pending (deferred) eigenvector update is a B round of identity rotations, which exchanges them back
+  if (lane < N / 2) *reinterpret_cast<double2*>(&CS[N + 2 * lane]) = make_double2(1.0, 0.0);
+  __syncwarp();
 
   int mypos = lane;        // register position of column `lane` (the diagonal element of this row)
   int colid = on ? lane : 0;   // column that sits at position `lane`
@@ -221,6 +238,7 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
       jacobi_round<N, 1>(a, v, S1, S0, CS, lane, rowoff, on, mypos, colid);
     }
   }
+  v_update<N, 1>(v, CS + N);      // flush the deferred update of the last B round
   if (info && lane == 0) info[mol] = sweeps;
   if (Vg) {
 #pragma unroll

@@ -1,0 +1,65 @@
+"""world_size-2 gloo test of the molecule sharding / gather host logic (no GPU)."""
+import os
+import socket
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world, port, nmol, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from pyseqm_b200.distributed import gather_molecules, shard_batch
+    species = torch.arange(nmol * 3).reshape(nmol, 3)
+    coords = torch.arange(nmol * 9, dtype=torch.float64).reshape(nmol, 3, 3)
+    sp, xyz, (lo, hi) = shard_batch(species, coords)
+    assert sp.shape[0] == hi - lo and torch.equal(xyz, coords[lo:hi])
+    energy = xyz.sum(dim=(1, 2)) * 2.0                      # stands for a per-molecule result
+    force = -xyz
+    e_all = gather_molecules(energy, nmol)
+    f_all = gather_molecules(force, nmol)
+    ok = torch.equal(e_all, coords.sum(dim=(1, 2)) * 2.0) and torch.equal(f_all, -coords)
+    q.put((rank, lo, hi, bool(ok)))
+    dist.destroy_process_group()
+
+
+def test_shard_bounds_cover_batch():
+    from pyseqm_b200.distributed import shard_bounds
+    for nmol in (0, 1, 7, 8, 1024, 1025):
+        for world in (1, 2, 3, 8):
+            b = shard_bounds(nmol, world)
+            assert b[0][0] == 0 and b[-1][1] == nmol
+            assert all(b[k][1] == b[k + 1][0] for k in range(world - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_shard_and_gather_world2_gloo():
+    world = 2
+    for nmol in (8, 7):                                    # even and ragged split
+        port = _free_port()
+        ctx = mp.get_context('spawn')
+        q = ctx.Queue()
+        procs = [ctx.Process(target=_worker, args=(r, world, port, nmol, q)) for r in range(world)]
+        for p in procs:
+            p.start()
+        res = sorted(q.get(timeout=120) for _ in range(world))
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        assert all(r[3] for r in res)
+        assert res[0][1] == 0 and res[0][2] == res[1][1] and res[1][2] == nmol
