@@ -154,8 +154,11 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
  *   P[B][n][n] in: initial guess, out: converged density; F out: fock(P) at the final density
  *   notconverged[B] out; niter[B] out (iterations taken by each molecule)
  *   iterations_out: int32[2] on the HOST = {iterations run, molecules still unconverged}
- *   work: seqm_scf_workspace(...) bytes.  Synchronises the stream once per iteration (convergence
- *   count), like the reference's notconverged.any(). */
+ *   work: seqm_scf_workspace(...) bytes.
+ * Two execution forms, same arithmetic: batches whose largest packed size is <= 32 with the eigh density and
+ * debug == 0 run the whole loop in ONE kernel (one warp per molecule, one stream synchronisation at the end);
+ * otherwise the host drives one iteration at a time and synchronises once per iteration (convergence count),
+ * like the reference's notconverged.any().  seqm_scf_fused(0) forces the second form (test hook). */
 typedef struct {
   int converger;      /* 0, 1, 2 */
   double alpha;       /* converger 0 */
@@ -165,6 +168,7 @@ typedef struct {
   int max_iter;
   int debug;          /* print "scf k max_err n_notconverged" like scf_loop.debug */
 } seqm_scf_options_t;
+void seqm_scf_fused(int on);
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);
 int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss,
              const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,

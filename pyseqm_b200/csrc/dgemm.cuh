@@ -22,4 +22,13 @@ int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, con
                      const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out,
                      int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st);
 
+double eigh_tolerance();
+size_t scf_small_scratch_bytes(int64_t nmol);
+int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, const double* g_ss, const double* g_pp,
+                     const double* g_sp, const double* g_p2, const double* h_sp, const int32_t* nheavy,
+                     const int32_t* nhydro, const int32_t* nocc, int mp, int converger, double alpha, double eps,
+                     int max_iter, double tol, double* P, double* F, double* E, uint8_t* nc, int32_t* niter,
+                     double* pairvec, double* Pold, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
+                     unsigned long long* stat, int32_t* mol_atom0, size_t nn, cudaStream_t st);
+
 }  // namespace seqm

@@ -203,6 +203,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
 }
 
 double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run
+double eigh_tolerance() { return g_eigh_tol; }
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {

@@ -15,6 +15,7 @@
 namespace seqm {
 
 constexpr int NFOCK = 5;
+int g_scf_fused = 1;      // 0: always the host-driven loop (test hook)
 
 enum MixMode { MIX_DIRECT = 0, MIX_CONST = 1, MIX_ADAPTIVE = 2, MIX_TAKE = 3 };
 
@@ -186,15 +187,17 @@ __global__ void init_flags_kernel(int nmol, uint8_t* nc, double* err, int32_t* n
 struct ScfWork {
   double *Pnew, *Pold, *Enew, *err, *G, *FOCK, *FPPF, *EMAT, *Vstore;
   unsigned long long* stat;
+  int32_t* mol_atom0;
   char* sp2;
-  size_t total;
+  size_t nn, total;      // nn = doubles per molecule in one matrix slab
 };
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt) {
   ScfWork w{};
-  const size_t nn = (size_t)16 * molsize * molsize;
+  const size_t nn = (size_t)16 * molsize * molsize > 64 ? (size_t)16 * molsize * molsize : 64;   // >= 8 x 8 (K3s)
+  w.nn = nn;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align256(bytes); return p; };
   w.Pnew = (double*)take(nmol * nn * 8);
@@ -202,6 +205,7 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
   w.Enew = (double*)take(nmol * 8);
   w.err = (double*)take(nmol * 8);
   w.stat = (unsigned long long*)take(64);
+  w.mol_atom0 = (int32_t*)take(scf_small_scratch_bytes(nmol));
   if (opt->converger == 2) {
     w.G = (double*)take(nmol * nn * 8);
     w.FOCK = (double*)take(nmol * NFOCK * nn * 8);
@@ -219,6 +223,8 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
 using namespace seqm;
 
 extern "C" {
+
+void seqm_scf_fused(int on) { g_scf_fused = on; }
 
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt) {
   if (!opt) return 0;
@@ -242,6 +248,22 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   ScfWork wk = carve((char*)work, B, S, opt);
   uint8_t* nc = notconverged;
   int rc;
+  const int mp_small = ((mmax < 1 ? 1 : mmax) + 1) & ~1;
+  if (!opt->use_sp2 && !opt->debug && mp_small <= 32 && g_scf_fused) {
+    // K3s: the whole loop in one launch, one warp per molecule
+    const int max_iter_s = opt->max_iter > 0 ? opt->max_iter : 1000;
+    SEQM_CUDA(cudaMemsetAsync(F, 0, (size_t)B * nn * 8, st));
+    SEQM_CUDA(cudaMemsetAsync(wk.stat, 0, 16, st));
+    rc = launch_scf_small(t, w, M, g_ss, g_pp, g_sp, g_p2, h_sp, nheavy, nhydro, nocc, mp_small, opt->converger,
+                          opt->alpha, opt->eps, max_iter_s, eigh_tolerance(), P, F, Eelec, nc, niter, pairvec, wk.Pold,
+                          wk.FOCK, wk.FPPF, wk.EMAT, wk.Vstore, wk.stat, wk.mol_atom0, wk.nn, st);
+    if (rc) return rc;
+    unsigned long long hs[2] = {0, 0};
+    SEQM_CUDA(cudaMemcpyAsync(hs, wk.stat, 16, cudaMemcpyDeviceToHost, st));
+    SEQM_CUDA(cudaStreamSynchronize(st));
+    if (iterations_out) { iterations_out[0] = (int32_t)hs[1]; iterations_out[1] = (int32_t)hs[0]; }
+    return SEQM_OK;
+  }
 
   prof_mark("scf_setup", st);
   SEQM_CUDA(cudaMemsetAsync(wk.Pnew, 0, (size_t)B * nn * 8, st));

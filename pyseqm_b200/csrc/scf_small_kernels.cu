@@ -1,0 +1,470 @@
+// K3s: the whole SCF loop of a small molecule (packed size m <= 32) in ONE kernel launch, one warp per molecule.
+// Molecules of a batch are independent (reference: every tensor of scf_loop.py carries the molecule as leading
+// batch index and converged molecules are frozen by the notconverged mask), so each warp runs the reference's
+// iteration schedule for its own molecule until that molecule converges: Fock build, energy, adaptive / Pulay
+// mixing, Jacobi eigensolver and density all work on packed m x m matrices in shared memory; the host is not
+// involved between iterations and nothing but the Pulay ring, the previous density and the eigenvector store
+// (all L2 resident) goes to global memory.
+// reference: seqm/seqm_functions/scf_loop.py:32-510, fock.py:6-139, energy.py:19-36, diag.py:102-172
+#include "eigh_warp.cuh"
+#include "dgemm.cuh"
+
+namespace seqm {
+
+#define KM(k) ((k) == 0 ? 0 : ((k) <= 2 ? 1 : ((k) <= 5 ? 2 : 3)))
+#define KN(k) ((k) - KM(k) * (KM(k) + 1) / 2)
+#define WT(k) ((KM(k) == KN(k)) ? 1.0 : 2.0)
+
+constexpr int SNFOCK = 5;
+enum SmallMix { SMIX_DIRECT = 0, SMIX_CONST = 1, SMIX_ADAPTIVE = 2, SMIX_TAKE = 3 };
+
+struct SmallScfArgs {
+  seqm_topology_t t;
+  seqm_w_t w;
+  const double *M, *gss, *gpp, *gsp, *gp2, *hsp;
+  const int32_t *nheavy, *nhydro, *nocc;
+  const int32_t* mol_atom0;      // [B+1] first real atom of every molecule
+  double *P, *F, *E;             // P in/out (padded), F out (padded, zero filled by the caller), E out
+  uint8_t* nc;
+  int32_t* niter;
+  double *pairvec, *Pold, *FOCK, *FPPF, *EMAT, *Vstore;
+  unsigned long long* stat;      // [0] molecules left unconverged, [1] largest iteration count
+  size_t nn;                     // doubles per molecule in Pold / one ring slot
+  int converger, max_iter;
+  double alpha, eps, tol;
+};
+
+__global__ void mol_atom0_kernel(int natoms, int nmol, const int32_t* __restrict__ atom_mol, int32_t* __restrict__ out) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a == 0) out[nmol] = natoms;
+  if (a >= natoms) return;
+  const int mol = atom_mol[a];
+  if (a == 0 || atom_mol[a - 1] != mol) out[mol] = a;
+}
+
+// exchange block and Coulomb vectors of one pair (fock.py:76-139); P and F packed in shared memory
+template <int CLS, int LD>
+__device__ __forceinline__ void small_fock_pair(const SmallScfArgs& A, int mol, int slot, int nh, int nh4,
+                                                const double* __restrict__ Ps, double* __restrict__ Fs) {
+  const seqm_topology_t& t = A.t;
+  const int p = t.cls_pairs[CLS][slot];
+  const int i = t.idxi[p], j = t.idxj[p];
+  const int S = (int)t.molsize;
+  const int si = t.atom_slot[i], sj = t.atom_slot[j];
+  const int oi = si < nh ? 4 * si : nh4 + si - nh, oj = sj < nh ? 4 * sj : nh4 + sj - nh;
+  const double* Mb = A.M + (((size_t)mol * S + si) * S + sj) * 16;
+  double* pv = A.pairvec + (size_t)p * 20;
+  constexpr int NA = (CLS == SEQM_CLS_HH) ? 1 : 10;
+  constexpr int NB = (CLS == SEQM_CLS_XX) ? 10 : 1;
+  constexpr int OA = (CLS == SEQM_CLS_HH) ? 1 : 4;
+  constexpr int OB = (CLS == SEQM_CLS_XX) ? 4 : 1;
+  double pA[NA], pB[NB];
+  {
+    const double* a = Ps + oi * LD + oi;
+    const double* b = Ps + oj * LD + oj;
+#pragma unroll
+    for (int k = 0; k < NA; ++k) pA[k] = WT(k) * a[KN(k) * LD + KM(k)];
+#pragma unroll
+    for (int l = 0; l < NB; ++l) pB[l] = WT(l) * b[KN(l) * LD + KM(l)];
+  }
+  double Pab[OA][OB];
+#pragma unroll
+  for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < OB; ++nu) Pab[mu][nu] = Ps[(oi + mu) * LD + oj + nu];
+  double toA[NA], toB[NB], Fab[OA][OB];
+#pragma unroll
+  for (int k = 0; k < NA; ++k) toA[k] = 0.0;
+#pragma unroll
+  for (int l = 0; l < NB; ++l) toB[l] = 0.0;
+#pragma unroll
+  for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < OB; ++nu) Fab[mu][nu] = 0.0;
+  const double* wc = CLS == SEQM_CLS_HH ? A.w.wHH : (CLS == SEQM_CLS_XH ? A.w.wXH : A.w.wXX);
+  const double* wp = (CLS == SEQM_CLS_HH) ? wc + slot : wc + ((size_t)(slot >> 5) * (NA * NB)) * 32 + (slot & 31);
+#pragma unroll
+  for (int k = 0; k < NA; ++k) {
+#pragma unroll
+    for (int l = 0; l < NB; ++l) {
+      const double wv = (CLS == SEQM_CLS_HH) ? wp[0] : wp[(size_t)(k * NB + l) * 32];
+      toA[k] += wv * pB[l];
+      toB[l] += pA[k] * wv;
+      const int m = KM(k), n = KN(k), a = KM(l), b = KN(l);
+      Fab[m][a] += Pab[n][b] * wv;
+      if (a != b) Fab[m][b] += Pab[n][a] * wv;
+      if (m != n) {
+        Fab[n][a] += Pab[m][b] * wv;
+        if (a != b) Fab[n][b] += Pab[m][a] * wv;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NA; ++k) pv[k] = toA[k];
+#pragma unroll
+  for (int l = 0; l < NB; ++l) pv[10 + l] = toB[l];
+#pragma unroll
+  for (int mu = 0; mu < OA; ++mu)
+#pragma unroll
+    for (int nu = 0; nu < OB; ++nu) {
+      const double f = Mb[mu * 4 + nu] - 0.5 * Fab[mu][nu];
+      Fs[(oi + mu) * LD + oj + nu] = f;
+      Fs[(oj + nu) * LD + oi + mu] = f;
+    }
+}
+
+template <int N>
+__global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ SmallScfArgs A) {
+  constexpr int LD = WarpLd<N>::value;
+  __shared__ __align__(16) double Ps[N * LD];
+  __shared__ __align__(16) double S0[N * LD];
+  __shared__ __align__(16) double S1[N * LD];
+  __shared__ __align__(16) double CS[2 * N];
+  const seqm_topology_t& t = A.t;
+  const int mol = blockIdx.x;
+  const int lane = threadIdx.x;
+  const int nh = A.nheavy[mol], nhy = A.nhydro[mol];
+  const int nh4 = 4 * nh, m = nh4 + nhy;
+  const int S = (int)t.molsize, n4 = 4 * S;
+  const size_t base = (size_t)mol * n4 * n4;
+  if (m <= 0) {
+    if (lane == 0) { A.nc[mol] = 0; A.niter[mol] = 0; A.E[mol] = 0.0; }
+    return;
+  }
+  const int no = A.nocc[mol];
+  const int atom0 = A.mol_atom0[mol], nat = A.mol_atom0[mol + 1] - atom0;
+  const int pair0 = t.start_i[atom0], pair1 = t.start_i[atom0 + nat];
+  // class ranges of this molecule's pairs (the pairs of one class are consecutive in that class's slot list)
+  int cls_lo[3], cls_n[3];
+  {
+    int lo[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff}, cnt[3] = {0, 0, 0};
+    for (int p = pair0 + lane; p < pair1; p += 32) {
+      const int c = t.pair_cls[p], s = t.pair_slot[p];
+#pragma unroll
+      for (int q = 0; q < 3; ++q)
+        if (c == q) { lo[q] = min(lo[q], s); ++cnt[q]; }
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        lo[q] = min(lo[q], __shfl_xor_sync(FULL, lo[q], o));
+        cnt[q] += __shfl_xor_sync(FULL, cnt[q], o);
+      }
+      cls_lo[q] = lo[q];
+      cls_n[q] = cnt[q];
+    }
+  }
+  double* Pold = A.Pold + (size_t)mol * A.nn;
+  double* FOCK = A.FOCK ? A.FOCK + (size_t)mol * SNFOCK * A.nn : nullptr;
+  double* FPPF = A.FPPF ? A.FPPF + (size_t)mol * SNFOCK * A.nn : nullptr;
+  double* EMAT = A.EMAT ? A.EMAT + (size_t)mol * 36 : nullptr;
+  double* Vg = A.Vstore + (size_t)mol * WV_LD * WV_LD;
+
+  // ---- P0 -> packed
+  for (int idx = lane; idx < N * LD; idx += 32) {
+    const int i = idx / LD, j = idx - i * LD;
+    Ps[idx] = (i < m && j < m) ? A.P[base + (size_t)pk2pd(i, nh4) * n4 + pk2pd(j, nh4)] : 0.0;
+  }
+  if (EMAT && lane == 0) {
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) EMAT[i * 6 + j] = (i > j) ? -1.0 : 0.0;
+  }
+  __syncwarp();
+
+  // F(Ps) -> S0, core Hamiltonian -> S1; returns 0.5 sum P (H + F)
+  auto fock = [&]() -> double {
+    for (int idx = lane; idx < N * LD; idx += 32) {
+      const int i = idx / LD, j = idx - i * LD;
+      double h = 0.0;
+      if (i < m && j < m) {
+        const int ai = i < nh4 ? i >> 2 : nh + i - nh4, mu = i < nh4 ? i & 3 : 0;
+        const int aj = j < nh4 ? j >> 2 : nh + j - nh4, nu = j < nh4 ? j & 3 : 0;
+        if (ai < aj || (ai == aj && mu <= nu)) h = A.M[(((size_t)mol * S + ai) * S + aj) * 16 + mu * 4 + nu];
+        else h = A.M[(((size_t)mol * S + aj) * S + ai) * 16 + nu * 4 + mu];
+      }
+      S1[idx] = h;
+      S0[idx] = h;
+    }
+    __syncwarp();
+    for (int s = lane; s < cls_n[2]; s += 32) small_fock_pair<SEQM_CLS_XX, LD>(A, mol, cls_lo[2] + s, nh, nh4, Ps, S0);
+    for (int s = lane; s < cls_n[1]; s += 32) small_fock_pair<SEQM_CLS_XH, LD>(A, mol, cls_lo[1] + s, nh, nh4, Ps, S0);
+    for (int s = lane; s < cls_n[0]; s += 32) small_fock_pair<SEQM_CLS_HH, LD>(A, mol, cls_lo[0] + s, nh, nh4, Ps, S0);
+    __syncwarp();
+    // diagonal blocks: one-centre terms + the Coulomb vectors of the atom's pairs in pair order
+    for (int q = lane; q < nat; q += 32) {
+      const int a = atom0 + q;
+      const bool heavy = t.Z[a] > 1;
+      const int s = t.atom_slot[a];
+      const int o = s < nh ? 4 * s : nh4 + s - nh;
+      double acc[10];
+#pragma unroll
+      for (int k = 0; k < 10; ++k) acc[k] = 0.0;
+      for (int r = t.start_i[a]; r < t.start_i[a + 1]; ++r) {
+        const double* pv = A.pairvec + (size_t)r * 20;
+        acc[0] += pv[0];
+        if (heavy) {
+#pragma unroll
+          for (int k = 1; k < 10; ++k) acc[k] += pv[k];
+        }
+      }
+      for (int r = t.start_j[a]; r < t.start_j[a + 1]; ++r) {
+        const double* pv = A.pairvec + (size_t)t.perm_j[r] * 20 + 10;
+        acc[0] += pv[0];
+        if (heavy) {
+#pragma unroll
+          for (int k = 1; k < 10; ++k) acc[k] += pv[k];
+        }
+      }
+      const double* Pd = Ps + o * LD + o;
+      double* Fd = S0 + o * LD + o;
+      const double GSS = A.gss[a], GPP = A.gpp[a], GSP = A.gsp[a], GP2 = A.gp2[a], HSP = A.hsp[a];
+      if (heavy) {
+        double Pu[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) Pu[k] = Pd[KN(k) * LD + KM(k)];
+        const double Pss = Pu[0], Ppp = Pu[2] + Pu[5] + Pu[9];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) {
+          const int mm = KM(k), n = KN(k);
+          double one;
+          if (k == 0) one = 0.5 * Pss * GSS + Ppp * (GSP - 0.5 * HSP);
+          else if (mm == n) one = Pss * (GSP - 0.5 * HSP) + 0.5 * Pu[k] * GPP + (Ppp - Pu[k]) * (1.25 * GP2 - 0.25 * GPP);
+          else if (n == 0) one = Pu[k] * (1.5 * HSP - 0.5 * GSP);
+          else one = Pu[k] * (0.75 * GPP - 1.25 * GP2);
+          const double f = Fd[n * LD + mm] + one + acc[k];      // Fd holds the core block
+          Fd[n * LD + mm] = f;
+          if (mm != n) Fd[mm * LD + n] = f;
+        }
+      } else {
+        Fd[0] = Fd[0] + 0.5 * Pd[0] * GSS + acc[0];
+      }
+    }
+    __syncwarp();
+    double e = 0.0;
+    for (int idx = lane; idx < m * m; idx += 32) {
+      const int i = idx / m, j = idx - i * m;
+      e += 0.5 * Ps[i * LD + j] * (S1[i * LD + j] + S0[i * LD + j]);
+    }
+    return warp_sum(e);
+  };
+
+  // P = mix(Pnew = S1, P = Ps, Pold)
+  auto mix = [&](int mode) {
+    double fac = 0.0;
+    if (mode == SMIX_ADAPTIVE) {
+      double num = 0.0, den = 0.0;
+      if (lane < m) {
+        const double dn = S1[lane * LD + lane], dc = Ps[lane * LD + lane], dold = Pold[lane * N + lane];
+        num = (dn - dc) * (dn - dc);
+        const double u = dn - dc * 2.0 + dold;
+        den = u * u;
+      }
+      num = warp_sum(num);
+      den = warp_sum(den);
+      fac = sqrt(num / den);
+    }
+    for (int idx = lane; idx < m * m; idx += 32) {
+      const int i = idx / m, j = idx - i * m;
+      const double pn = S1[i * LD + j], pc = Ps[i * LD + j];
+      double out;
+      if (mode == SMIX_DIRECT) { Pold[i * N + j] = pc; out = pn; }
+      else if (mode == SMIX_CONST) out = A.alpha * pc + (1.0 - A.alpha) * pn;
+      else if (mode == SMIX_ADAPTIVE) { Pold[i * N + j] = pc; out = (1.0 + fac) * pn - fac * pc; }
+      else out = pn;
+      Ps[i * LD + j] = out;
+    }
+    __syncwarp();
+  };
+
+  // Pulay store (scf_loop.py:408-470): FOCK[c] = F, FPPF[c] = triu(FP - PF), EMAT[c][s] = <FPPF[c], FPPF[s]>
+  auto pulay_store = [&](int c, int cF) {
+    const bool on = lane < N;
+    const int rowoff = (on ? lane : 0) * LD;
+    double g[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) g[j] = 0.0;
+#pragma unroll 2
+    for (int k = 0; k < N; ++k) {
+      const double fk = on ? S0[rowoff + k] : 0.0;
+#pragma unroll
+      for (int jj = 0; jj < N / 2; ++jj) {
+        const double2 w2 = *reinterpret_cast<const double2*>(&Ps[k * LD + 2 * jj]);
+        g[2 * jj] = fma(fk, w2.x, g[2 * jj]);
+        g[2 * jj + 1] = fma(fk, w2.y, g[2 * jj + 1]);
+      }
+    }
+    if (on) {
+#pragma unroll
+      for (int jj = 0; jj < N / 2; ++jj)
+        *reinterpret_cast<double2*>(&S1[rowoff + 2 * jj]) = make_double2(g[2 * jj], g[2 * jj + 1]);
+    }
+    __syncwarp();
+    double* fo = FOCK + (size_t)c * A.nn;
+    double* fp = FPPF + (size_t)c * A.nn;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      g[j] = (on && j >= lane) ? g[j] - S1[j * LD + lane] : 0.0;
+      if (on) {
+        fp[lane * N + j] = g[j];
+        fo[lane * N + j] = S0[rowoff + j];
+      }
+    }
+    for (int s = 0; s < cF; ++s) {
+      const double* other = FPPF + (size_t)s * A.nn;
+      double acc = 0.0;
+      if (on && s != c) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc = fma(g[j], other[lane * N + j], acc);
+      } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc = fma(g[j], g[j], acc);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0) EMAT[c * 6 + s] = acc;
+    }
+    __syncwarp();
+  };
+
+  // F = sum_s coeff_s FOCK[s] with the DIIS coefficients of the reference (scf_loop.py:471-496) -> S0
+  auto pulay_extrapolate = [&](int c, int cF) {
+    double x[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (lane == 0) {
+      const int d = cF + 1;
+      double a[6][7];
+      for (int i = 0; i < 6; ++i)
+        for (int j = 0; j < 6; ++j) a[i][j] = EMAT[i * 6 + j] + (j > i ? EMAT[j * 6 + i] : 0.0);
+      const double sc = a[c][c];
+      for (int i = 0; i < cF; ++i)
+        for (int j = 0; j < cF; ++j) a[i][j] = a[i][j] / sc;
+      for (int i = 0; i < d; ++i) a[i][6] = (i == d - 1) ? 1.0 : 0.0;
+      for (int cc = 0; cc < d; ++cc) {
+        int piv = cc;
+        double best = fabs(a[cc][cc]);
+        for (int r = cc + 1; r < d; ++r)
+          if (fabs(a[r][cc]) > best) { best = fabs(a[r][cc]); piv = r; }
+        if (piv != cc) {
+          for (int j = 0; j < 7; ++j) { const double tmp = a[cc][j]; a[cc][j] = a[piv][j]; a[piv][j] = tmp; }
+        }
+        const double inv = 1.0 / a[cc][cc];
+        for (int r = cc + 1; r < d; ++r) {
+          const double f = a[r][cc] * inv;
+          for (int j = cc; j < d; ++j) a[r][j] -= f * a[cc][j];
+          a[r][6] -= f * a[cc][6];
+        }
+      }
+      for (int r = d - 1; r >= 0; --r) {
+        double sum = a[r][6];
+        for (int j = r + 1; j < d; ++j) sum -= a[r][j] * x[j];
+        x[r] = sum / a[r][r];
+      }
+    }
+    double coeff[SNFOCK];
+#pragma unroll
+    for (int s = 0; s < SNFOCK; ++s) coeff[s] = -__shfl_sync(FULL, x[s], 0);
+    for (int idx = lane; idx < N * N; idx += 32) {
+      const int i = idx / N, j = idx - i * N;
+      double acc = 0.0;
+      for (int s = 0; s < cF; ++s) acc += FOCK[(size_t)s * A.nn + idx] * coeff[s];
+      S0[i * LD + j] = acc;
+    }
+    __syncwarp();
+  };
+
+  // The reference's schedule (scf_loop.py: scf_forward0/1/2) as one loop with a single call site per phase.
+  // k = iterations completed.  converger 2: iterations 0,1 direct, 2 adaptive, 3,4 plain (the states after
+  // iterations 2 and 3 enter the Pulay ring), from 5 on the Fock matrix is the DIIS extrapolation of the ring and
+  // every new state is stored.
+  double E = 0.0;
+  int k = -1, counter = -1, cF = 0;
+  bool nc = true;
+  for (;;) {
+    const double en = fock();
+    if (k < 0) {
+      E = en;
+      k = 0;
+    } else {
+      if (A.converger == 2 && (k == 2 || k == 3 || k >= 5)) {
+        cF = cF < SNFOCK ? cF + 1 : SNFOCK;
+        counter = (counter + 1) % SNFOCK;
+        pulay_store(counter, cF);
+      }
+      const double err = fabs(en - E);
+      E = en;
+      ++k;
+      nc = err > A.eps;
+      if (k >= A.max_iter && (A.converger == 0 || (A.converger == 1 && k >= 3) || (A.converger == 2 && k >= 6))) break;
+    }
+    if (!nc) break;
+    int mode;
+    if (A.converger == 0) mode = SMIX_CONST;
+    else if (k < 2) mode = SMIX_DIRECT;
+    else if (A.converger == 1 || k == 2) mode = SMIX_ADAPTIVE;
+    else mode = SMIX_TAKE;
+    if (A.converger == 2 && k >= 5) pulay_extrapolate(counter, cF);
+    warp_eigh_density<N>(S0, S1, CS, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr);
+    mix(mode);
+  }
+
+  // ---- results back to the padded layout
+  for (int idx = lane; idx < m * m; idx += 32) {
+    const int i = idx / m, j = idx - i * m;
+    const size_t g = base + (size_t)pk2pd(i, nh4) * n4 + pk2pd(j, nh4);
+    A.P[g] = Ps[i * LD + j];
+    A.F[g] = S0[i * LD + j];
+  }
+  if (lane == 0) {
+    A.E[mol] = E;
+    A.nc[mol] = nc ? 1 : 0;
+    A.niter[mol] = k;
+    if (nc) atomicAdd(&A.stat[0], 1ULL);
+    atomicMax(&A.stat[1], (unsigned long long)k);
+  }
+}
+
+template <int N>
+static int launch_small_n(int64_t nmol, const SmallScfArgs& args, cudaStream_t st) {
+  static thread_local bool configured = false;
+  if (!configured) {
+    SEQM_CUDA(cudaFuncSetAttribute(scf_small_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                   (int)cudaSharedmemCarveoutMaxShared));
+    configured = true;
+  }
+  scf_small_kernel<N><<<(unsigned)nmol, 32, 0, st>>>(args);
+  SEQM_CHECK_LAUNCH("scf_small_kernel");
+  return SEQM_OK;
+}
+
+size_t scf_small_scratch_bytes(int64_t nmol) { return (size_t)(nmol + 1) * sizeof(int32_t); }
+
+// whole SCF for a batch whose largest packed size is <= 32; stat[0..1] must be zero on entry
+int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, const double* g_ss, const double* g_pp,
+                     const double* g_sp, const double* g_p2, const double* h_sp, const int32_t* nheavy,
+                     const int32_t* nhydro, const int32_t* nocc, int mp, int converger, double alpha, double eps,
+                     int max_iter, double tol, double* P, double* F, double* E, uint8_t* nc, int32_t* niter,
+                     double* pairvec, double* Pold, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
+                     unsigned long long* stat, int32_t* mol_atom0, size_t nn, cudaStream_t st) {
+  prof_mark("scf_small", st);
+  mol_atom0_kernel<<<cdiv(t.natoms > 0 ? t.natoms : 1, 256), 256, 0, st>>>((int)t.natoms, (int)t.nmol, t.atom_mol, mol_atom0);
+  SEQM_CHECK_LAUNCH("mol_atom0_kernel");
+  SmallScfArgs a{};
+  a.t = t; a.w = w; a.M = M; a.gss = g_ss; a.gpp = g_pp; a.gsp = g_sp; a.gp2 = g_p2; a.hsp = h_sp;
+  a.nheavy = nheavy; a.nhydro = nhydro; a.nocc = nocc; a.mol_atom0 = mol_atom0;
+  a.P = P; a.F = F; a.E = E; a.nc = nc; a.niter = niter; a.pairvec = pairvec; a.Pold = Pold; a.FOCK = FOCK;
+  a.FPPF = FPPF; a.EMAT = EMAT; a.Vstore = Vstore; a.stat = stat; a.nn = nn; a.converger = converger;
+  a.max_iter = max_iter; a.alpha = alpha; a.eps = eps; a.tol = tol;
+  int rc;
+#define SEQM_SMALL_CASE(NN) if (mp <= NN) { rc = launch_small_n<NN>(t.nmol, a, st); prof_mark("end", st); return rc; }
+  SEQM_SMALL_CASE(8)
+  SEQM_SMALL_CASE(12)
+  SEQM_SMALL_CASE(16)
+  SEQM_SMALL_CASE(20)
+  SEQM_SMALL_CASE(24)
+  SEQM_SMALL_CASE(28)
+  SEQM_SMALL_CASE(30)
+  SEQM_SMALL_CASE(32)
+#undef SEQM_SMALL_CASE
+  return fail(SEQM_EUNSUPPORTED, "launch_scf_small: packed size above 32");
+}
+
+}  // namespace seqm
