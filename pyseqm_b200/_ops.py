@@ -99,7 +99,7 @@ def elec_energy(P, F, M, nmol, molsize, D=None):
     return E
 
 
-def eigh_density(F, nheavy, nhydro, nocc, molsize, mmax, want_eig=False, active=None):
+def eigh_density(F, nheavy, nhydro, nocc, molsize, mmax, want_eig=False, active=None, info=None):
     """-> P (and e[B,n], v[B,n,n] with the packed eigenvectors in the top-left m x m corner)"""
     F = _f64(F)
     B, n4 = F.shape[0], F.shape[1]
@@ -107,7 +107,7 @@ def eigh_density(F, nheavy, nhydro, nocc, molsize, mmax, want_eig=False, active=
     e = torch.zeros(B, n4, dtype=torch.float64, device=F.device) if want_eig else None
     v = torch.zeros_like(F) if want_eig else None
     check(lib().seqm_eigh_density(B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc), _p(active), _p(P),
-                                  _p(e), _p(v), _p(None), _stream()), 'seqm_eigh_density')
+                                  _p(e), _p(v), _p(info), _stream()), 'seqm_eigh_density')
     return (P, e, v) if want_eig else P
 
 

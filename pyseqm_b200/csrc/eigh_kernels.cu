@@ -202,8 +202,9 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
   }
 }
 
-double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run
-double eigh_tolerance() { return g_eigh_tol; }
+double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel)
+double g_eigh_tol_warp = 1.0e-18; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
+double eigh_tolerance() { return g_eigh_tol_warp; }
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {
@@ -244,7 +245,7 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   prof_mark("eigh_density", st);
   int rc;
   if (mp <= 32 && !g_force_block_jacobi)
-    rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol, st);
+    rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 32)
     rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else if (mp <= 64)
@@ -264,7 +265,10 @@ extern "C" {
 int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
 void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
 
-void seqm_eigh_tolerance(double tol) { g_eigh_tol = tol > 0.0 ? tol : 1.0e-24; }
+void seqm_eigh_tolerance(double tol) {
+  g_eigh_tol = tol > 0.0 ? tol : 1.0e-24;
+  g_eigh_tol_warp = tol > 0.0 ? tol : 1.0e-18;
+}
 
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,

@@ -7,11 +7,17 @@
 // column order is reversed and every pair of columns has met exactly once (one sweep); all register indices
 // are compile-time constants.  The row half of the similarity transform needs the partner row: rows are
 // published in shared memory once per round (double buffered) and read back with 128-bit loads; the N/2
-// (c,s) pairs of a round travel through shared memory as well.  Per round and lane: 6N FP64 operations,
+// rotation coefficients of a round travel through shared memory as well.  Rotations are applied in the scaled
+// (fast Givens) form, one FMA per element.  Per round and lane: 3N FP64 operations + ~40 for the rotation,
 // ~1.5N + 4 shared-memory instructions, two warp shuffles (position bookkeeping), two __syncwarp.
+// Shared memory per warp: two row buffers N x LD and CS[4N] (rotation coefficients, scales, position table).
 // reference: seqm/seqm_functions/diag.py:102-172 (sym_eig_trunc), pack.py:7-41
 #pragma once
 #include "abi_common.cuh"
+
+#ifndef SEQM_TICK
+#define SEQM_TICK(i)      // tools/time_round.cu defines this to sample clock64() inside a round
+#endif
 
 namespace seqm {
 
@@ -38,40 +44,62 @@ template <int N, int PAR> __device__ __forceinline__ int mate_of(int x) {
   return (x == 0 || x == N - 1) ? x : ((x & 1) ? x + 1 : x - 1);
 }
 
-// V <- V J for a round of parity PAR whose (c,s) pairs are in CSp (the columns of every pair change places)
-template <int N, int PAR>
-__device__ __forceinline__ void v_update(double (&v)[N], const double* __restrict__ CSp) {
-  constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
-#pragma unroll
-  for (int k = 0; k < NPAIR; ++k) {
-    const double2 cs = *reinterpret_cast<const double2*>(&CSp[2 * k]);
-    const int j0 = 2 * k + PAR, j1 = j0 + 1;
-    const double v0 = v[j0], v1 = v[j1];
-    v[j1] = cs.x * v0 - cs.y * v1;
-    v[j0] = cs.y * v0 + cs.x * v1;
+// The schedule of a sweep does not depend on the data: TAB[r][lane] describes round r for the row `lane` when the
+// sweep starts from the identity arrangement (column id j at position j):
+//   bits 0-4 partner row, bits 5-9 left position L of the pair, bit 10 this row is the left member, bit 11 active.
+// A sweep reverses the arrangement; the next sweep is the mirror image (same partners, L -> N-2-L, left <-> right)
+// and restores the identity, so one table of N rounds serves all sweeps.
+template <int N>
+__device__ __forceinline__ void build_schedule(unsigned short* __restrict__ TAB, int lane) {
+  const bool on = lane < N;
+  int mypos = lane, colid = on ? lane : 0;
+#pragma unroll 1
+  for (int r = 0; r < N; ++r) {
+    const int mp = (r & 1) ? mate_of<N, 1>(mypos) : mate_of<N, 0>(mypos);
+    const int ml = (r & 1) ? mate_of<N, 1>(lane) : mate_of<N, 0>(lane);
+    const bool act = mp != mypos, left = mypos < mp;
+    const int L = (on && act) ? (left ? mypos : mp) : 0;
+    const int partner = __shfl_sync(FULL, colid, mp & 31);
+    TAB[r * 32 + lane] = (unsigned short)(partner | (L << 5) | ((act && left) ? 1 << 10 : 0) | (act ? 1 << 11 : 0));
+    colid = __shfl_sync(FULL, colid, ml & 31);
+    mypos = mp;
   }
+  __syncwarp();
 }
 
-// one round; Sr = row buffer holding the current A, Sw = buffer that receives the updated rows.
-// CS = [2][N]: (c,s) pairs of the last A round and of the last B round.  The eigenvector update of the PREVIOUS
-// round is executed here, next to the (long, dependent) rotation computation, so that the FP64 pipe has
-// independent work while that chain runs.
+// 1/sqrt(q) for q in [1, 2] without the special-case branches of rsqrt(): hardware seed + one cubic step
+__device__ __forceinline__ double rsqrt_unit(double q) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(q));
+  const double e = fma(-q * y, y, 1.0);
+  return fma(y * e, fma(0.375, e, 0.5), y);
+}
+
+// One round.  Sr = row buffer holding the current (scaled) A, Sw = buffer that receives the updated rows.
+// Rotations are applied in the scaled ("fast Givens") form: the true matrix is D A~ D and the true eigenvector
+// matrix V~ D with one scale d per column id, a rotation (c, s = t c) of the columns p, q becomes
+//   a~_p <- a~_p - tp a~_q,  a~_q <- a~_q + tq a~_p,   tp = t d_q/d_p, tq = t d_p/d_q,   d_p, d_q <- c d_p, c d_q
+// i.e. ONE fused multiply-add per element instead of a multiply and an FMA.  The scales are folded back into
+// A~, V~ at the end of every sweep (renormalise()), so they stay in [0.7^N, 1].
+// CS[N]: (tp, tq) of the pairs of this round; DSC[id] = (d, 1/d); tab = this round's schedule entry, sigma = 1 in
+// the mirrored (odd) sweeps.  The round is branch free.
 template <int N, int PAR>
 __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], const double* __restrict__ Sr,
-                                             double* __restrict__ Sw, double* __restrict__ CS, int lane, int rowoff,
-                                             bool on, int& mypos, int& colid) {
+                                             double* __restrict__ Sw, double* __restrict__ CS,
+                                             double2* __restrict__ DSC, unsigned tab, int sigma, int lane, int rowoff,
+                                             bool on, double& dmy, double& idmy) {
   constexpr int LD = WarpLd<N>::value;
   constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
-  double* CSc = CS + PAR * N;
-  const double* CSp = CS + (1 - PAR) * N;
-  const int mp = mate_of<N, PAR>(mypos);
-  const bool act = mp != mypos;
-  const bool left = mypos < mp;
-  const int L = on ? (left ? mypos : mp) : 0;               // left position of my pair (own position when idle)
-  const int partner = __shfl_sync(FULL, colid, mp & 31);    // row that owns the column at the mate position
+  SEQM_TICK(0);
+  const int partner = tab & 31;
+  const bool act = (tab >> 11) & 1;
+  const bool left = (((tab >> 10) & 1) != sigma) && act;
+  const int L0 = (tab >> 5) & 31;
+  const int L = (sigma && on) ? N - 2 - L0 : L0;
   const int prow = partner * LD;
   const double x0 = Sr[rowoff + L], x1 = Sr[rowoff + L + 1];
   const double y0 = Sr[prow + L], y1 = Sr[prow + L + 1];
+  const double2 dpn = DSC[partner];
   double b[N];
 #pragma unroll
   for (int jj = 0; jj < N / 2; ++jj) {
@@ -79,47 +107,84 @@ __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], con
     b[2 * jj] = t.x;
     b[2 * jj + 1] = t.y;
   }
-  v_update<N, 1 - PAR>(v, CSp);
-  // rotation: with r = 1/sqrt(d^2+b^2), u = (1 + |d| r)/2 = cos^2, c = sqrt(u), s = +-|b| r / (2c); branch free,
-  // two rsqrt, and c^2 + s^2 = 1 to rounding whatever the accuracy of r
-  const double app = left ? x0 : y0, apq = left ? x1 : y1, aqq = left ? y1 : x1;
-  const double d = aqq - app, bb = 2.0 * apq;
-  const double h2 = fmax(d * d + bb * bb, 1.0e-300);
-  const double r = rsqrt(h2);
-  const double u = 0.5 + 0.5 * fabs(d) * r;
-  const double w = rsqrt(u);
-  const bool rot = act && apq != 0.0;
-  const double c = rot ? u * w : 1.0;
-  const double sa = 0.5 * fabs(bb) * r * w;
-  const double s = rot ? (((d >= 0.0) == (bb >= 0.0)) ? sa : -sa) : 0.0;
-  if (act && left) *reinterpret_cast<double2*>(&CSc[2 * (L >> 1)]) = make_double2(c, s);
+  // Rotation from the TRUE 2x2 block (app, apq; apq, aqq).  The tangent t = sgn(d) b / (|d| + sqrt(d^2 + b^2)),
+  // d = aqq - app, b = 2 apq, is evaluated in FP32: its error (1e-7 relative) only leaves a residual 1e-7 |apq|
+  // behind the rotation, i.e. costs nothing until the off-diagonal norm is at 1e-8 of the matrix norm.  The
+  // rotation stays orthogonal to FP64 rounding because c = 1/sqrt(1 + t^2) is computed in FP64 from that same t
+  // (needed for the scales only, off the critical path of the round).
+  const double dP = left ? dmy : dpn.x, iP = left ? idmy : dpn.y;
+  const double dQ = left ? dpn.x : dmy, iQ = left ? dpn.y : idmy;
+  const double apq_s = left ? x1 : y1;
+  const double app = dP * dP * (left ? x0 : y0), apq = dP * dQ * apq_s, aqq = dQ * dQ * (left ? y1 : x1);
+  const double rqp = dQ * iP, rpq = dP * iQ;
+  const float df = (float)(aqq - app), bf = (float)(2.0 * apq);
+  const float h2 = fmaxf(fmaf(df, df, bf * bf), 1.0e-37f);
+  const float den = fmaxf(fmaf(h2, __frsqrt_rn(h2), fabsf(df)), 1.0e-37f);
+  float tf = __fdividef(df >= 0.0f ? bf : -bf, den);
+  tf = fminf(fmaxf(tf, -1.0f), 1.0f);
+  const double t = (act && apq_s != 0.0) ? (double)tf : 0.0;
+  const double tp = t * rqp, tq = t * rpq;
+  {
+    const double q = fma(t, t, 1.0);
+    const double c = rsqrt_unit(q);
+    dmy *= c;
+    idmy *= q * c;
+  }
+  SEQM_TICK(1);
+  if (left) *reinterpret_cast<double2*>(&CS[2 * (L >> 1)]) = make_double2(tp, tq);
   __syncwarp();
-  // rows: A <- J^T A   (row p: c*row_p - s*row_q, row q: s*row_p + c*row_q)
-  const double sg = left ? -s : s;
+  SEQM_TICK(2);
+  if (on) DSC[lane] = make_double2(dmy, idmy);
+  // rows: row p <- row p - tp row q, row q <- row q + tq row p
+  const double sg = left ? -tp : tq;
 #pragma unroll
-  for (int j = 0; j < N; ++j) a[j] = c * a[j] + sg * b[j];
-  // columns: A <- A J with the swap
+  for (int j = 0; j < N; ++j) a[j] = fma(sg, b[j], a[j]);
+  SEQM_TICK(3);
+  // columns of A and V, and the two columns of every pair change places
 #pragma unroll
   for (int k = 0; k < NPAIR; ++k) {
-    const double2 cs = *reinterpret_cast<const double2*>(&CSc[2 * k]);
+    const double2 cs = *reinterpret_cast<const double2*>(&CS[2 * k]);
     const int j0 = 2 * k + PAR, j1 = j0 + 1;
     const double a0 = a[j0], a1 = a[j1];
-    a[j1] = cs.x * a0 - cs.y * a1;
-    a[j0] = cs.y * a0 + cs.x * a1;
+    a[j1] = fma(-cs.x, a1, a0);
+    a[j0] = fma(cs.y, a0, a1);
+    const double v0 = v[j0], v1 = v[j1];
+    v[j1] = fma(-cs.x, v1, v0);
+    v[j0] = fma(cs.y, v0, v1);
   }
+  SEQM_TICK(4);
   if (on) {
 #pragma unroll
     for (int jj = 0; jj < N / 2; ++jj)
       *reinterpret_cast<double2*>(&Sw[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
   }
-  colid = __shfl_sync(FULL, colid, mate_of<N, PAR>(lane) & 31);
-  mypos = mp;
+  SEQM_TICK(5);
   __syncwarp();
+  SEQM_TICK(6);
 }
 
-// column index that the first (fake) pending B-round update maps to position j
-template <int N> __host__ __device__ constexpr int preswap(int j) {
-  return (j == 0 || j >= N - 1) ? j : ((j & 1) ? j + 1 : j - 1);
+// fold the scales back into A~ and V~ (true values again), reset them to one and publish the rows in S;
+// sigma = arrangement after the sweep (1: column id N-1-j at position j)
+template <int N>
+__device__ __forceinline__ void renormalise(double (&a)[N], double (&v)[N], double* __restrict__ S,
+                                            double2* __restrict__ DSC, int sigma, int lane, int rowoff, bool on,
+                                            double& dmy, double& idmy) {
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
+    const double dj = DSC[sigma ? N - 1 - j : j].x;
+    a[j] *= dmy * dj;
+    v[j] *= dj;
+  }
+  dmy = 1.0;
+  idmy = 1.0;
+  __syncwarp();
+  if (on) {
+    DSC[lane] = make_double2(1.0, 1.0);
+#pragma unroll
+    for (int jj = 0; jj < N / 2; ++jj)
+      *reinterpret_cast<double2*>(&S[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
+  }
+  __syncwarp();
 }
 
 // Eigen-decomposition of one packed symmetric matrix by one warp, and the density matrix of its lowest `no`
@@ -130,9 +195,9 @@ template <int N> __host__ __device__ constexpr int preswap(int j) {
 //        may be null) in the reference's sorted order; returns the number of sweeps
 template <int N>
 __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double* __restrict__ S1,
-                                                 double* __restrict__ CS, double* __restrict__ Vg, int warm,
-                                                 double tol, int m, int no, int n4, double* __restrict__ e_out,
-                                                 double* __restrict__ v_out) {
+                                                 double* __restrict__ CS, const unsigned short* __restrict__ TAB,
+                                                 double* __restrict__ Vg, int warm, double tol, int m, int no,
+                                                 int n4, double* __restrict__ e_out, double* __restrict__ v_out) {
   constexpr int LD = WarpLd<N>::value;
   const int lane = threadIdx.x & 31;
   const bool on = lane < N;
@@ -152,7 +217,7 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
       if (on) S1[r * LD + lane] = Vg[r * WV_LD + lane];
     __syncwarp();
 #pragma unroll
-    for (int j = 0; j < N; ++j) v[j] = on ? S1[rowoff + preswap<N>(j)] : 0.0;
+    for (int j = 0; j < N; ++j) v[j] = on ? S1[rowoff + j] : 0.0;
     // T = A V0 : row `lane`
     double t[N];
 #pragma unroll
@@ -195,18 +260,19 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     __syncwarp();
   } else {
 #pragma unroll
-    for (int j = 0; j < N; ++j) v[j] = (preswap<N>(j) == lane) ? 1.0 : 0.0;
+    for (int j = 0; j < N; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
   }
-  // S0 holds the rows of the current A; v is stored with the column pairs of a B round exchanged and the
-  // pending (deferred) eigenvector update is a B round of identity rotations, which exchanges them back
-  if (lane < N / 2) *reinterpret_cast<double2*>(&CS[N + 2 * lane]) = make_double2(1.0, 0.0);
+  // S0 holds the rows of the current A
+  double2* DSC = reinterpret_cast<double2*>(CS + N);      // [N] (d, 1/d) per column id
+  if (on) DSC[lane] = make_double2(1.0, 1.0);
+  double dmy = 1.0, idmy = 1.0;
   __syncwarp();
 
-  int mypos = lane;        // register position of column `lane` (the diagonal element of this row)
-  int colid = on ? lane : 0;   // column that sits at position `lane`
+  int sigma = 0;           // 0: column id j at position j, 1: reversed (after an odd number of sweeps)
   int sweeps = 0;
   bool last = false;
   for (; sweeps < WARP_MAX_SWEEPS; ++sweeps) {
+    const int mypos = sigma ? N - 1 - lane : lane;      // position of the diagonal element of this row
     double off = 0.0, tot = 0.0;
 #pragma unroll
     for (int j = 0; j < N; ++j) {
@@ -218,12 +284,16 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     tot = warp_sum(tot);
     if (off == 0.0 || last) break;
     if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
+#pragma unroll 1
     for (int r = 0; r < N; r += 2) {
-      jacobi_round<N, 0>(a, v, S0, S1, CS, lane, rowoff, on, mypos, colid);
-      jacobi_round<N, 1>(a, v, S1, S0, CS, lane, rowoff, on, mypos, colid);
+      const unsigned t0 = TAB[r * 32 + lane], t1 = TAB[(r + 1) * 32 + lane];
+      jacobi_round<N, 0>(a, v, S0, S1, CS, DSC, t0, sigma, lane, rowoff, on, dmy, idmy);
+      jacobi_round<N, 1>(a, v, S1, S0, CS, DSC, t1, sigma, lane, rowoff, on, dmy, idmy);
     }
+    sigma ^= 1;
+    renormalise<N>(a, v, S0, DSC, sigma, lane, rowoff, on, dmy, idmy);
   }
-  v_update<N, 1>(v, CS + N);      // flush the deferred update of the last B round
+  const int colid = on ? (sigma ? N - 1 - lane : lane) : 0;      // column id at position `lane`
   if (Vg) {
 #pragma unroll
     for (int jj = 0; jj < N / 2; ++jj)

@@ -23,7 +23,9 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   const bool on = lane < N;
   __shared__ __align__(16) double S0[N * LD];
   __shared__ __align__(16) double S1[N * LD];
-  __shared__ __align__(16) double CS[2 * N];
+  __shared__ __align__(16) double CS[3 * N];
+  __shared__ unsigned short TAB[N * 32];
+  build_schedule<N>(TAB, lane);
   // ---- load the packed matrix (upper triangle, like eigh(UPLO='U')) through shared memory
   for (int r = 0; r < N; ++r) {
     double x = 0.0;
@@ -36,7 +38,7 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   __syncwarp();
   __syncwarp();
   double* Vg = Vstore ? Vstore + (size_t)mol * WV_LD * WV_LD : nullptr;
-  const int sweeps = warp_eigh_density<N>(S0, S1, CS, Vg, warm, tol, m, nocc[mol], n4,
+  const int sweeps = warp_eigh_density<N>(S0, S1, CS, TAB, Vg, warm, tol, m, nocc[mol], n4,
                                           e_out ? e_out + (size_t)mol * n4 : nullptr, v_out ? v_out + base : nullptr);
   if (info && lane == 0) info[mol] = sweeps;
   for (int i2 = 0; i2 < m; ++i2)

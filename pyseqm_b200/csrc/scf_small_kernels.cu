@@ -119,7 +119,8 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   __shared__ __align__(16) double Ps[N * LD];
   __shared__ __align__(16) double S0[N * LD];
   __shared__ __align__(16) double S1[N * LD];
-  __shared__ __align__(16) double CS[2 * N];
+  __shared__ __align__(16) double CS[3 * N];
+  __shared__ unsigned short TAB[N * 32];
   const seqm_topology_t& t = A.t;
   const int mol = blockIdx.x;
   const int lane = threadIdx.x;
@@ -161,6 +162,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   double* EMAT = A.EMAT ? A.EMAT + (size_t)mol * 36 : nullptr;
   double* Vg = A.Vstore + (size_t)mol * WV_LD * WV_LD;
 
+  build_schedule<N>(TAB, lane);
   // ---- P0 -> packed
   for (int idx = lane; idx < N * LD; idx += 32) {
     const int i = idx / LD, j = idx - i * LD;
@@ -402,7 +404,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     else if (A.converger == 1 || k == 2) mode = SMIX_ADAPTIVE;
     else mode = SMIX_TAKE;
     if (A.converger == 2 && k >= 5) pulay_extrapolate(counter, cF);
-    warp_eigh_density<N>(S0, S1, CS, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr);
+    warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr);
     mix(mode);
   }
 
