@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libseqm_b200.so')
+LIB_PATH = os.environ.get('SEQM_B200_LIB') or os.path.join(_HERE, 'libseqm_b200.so')      # env: instrumented builds
 
 c_i32p = ctypes.POINTER(ctypes.c_int32)
 c_f64p = ctypes.POINTER(ctypes.c_double)

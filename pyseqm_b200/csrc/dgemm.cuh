@@ -28,7 +28,7 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
                      const double* g_sp, const double* g_p2, const double* h_sp, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, int mp, int converger, double alpha, double eps,
                      int max_iter, double tol, double* P, double* F, double* E, uint8_t* nc, int32_t* niter,
-                     double* pairvec, double* Pold, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
+                     double* pairvec, double* Pold, double* Hpk, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
                      unsigned long long* stat, int32_t* mol_atom0, size_t nn, cudaStream_t st);
 
 }  // namespace seqm

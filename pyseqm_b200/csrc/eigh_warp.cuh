@@ -15,6 +15,9 @@
 #pragma once
 #include "abi_common.cuh"
 
+#ifndef SEQM_PHASE
+#define SEQM_PHASE(i)     // timing builds (tools/build_timing.sh) accumulate clock64() per phase of molecule 0
+#endif
 #ifndef SEQM_TICK
 #define SEQM_TICK(i)      // tools/time_round.cu defines this to sample clock64() inside a round
 #endif
@@ -262,6 +265,7 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
 #pragma unroll
     for (int j = 0; j < N; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
   }
+  SEQM_PHASE(7);
   // S0 holds the rows of the current A
   double2* DSC = reinterpret_cast<double2*>(CS + N);      // [N] (d, 1/d) per column id
   if (on) DSC[lane] = make_double2(1.0, 1.0);
@@ -293,6 +297,7 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     sigma ^= 1;
     renormalise<N>(a, v, S0, DSC, sigma, lane, rowoff, on, dmy, idmy);
   }
+  SEQM_PHASE(8);
   const int colid = on ? (sigma ? N - 1 - lane : lane) : 0;      // column id at position `lane`
   if (Vg) {
 #pragma unroll
@@ -352,6 +357,7 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
   }
   __syncwarp();
   __syncwarp();
+  SEQM_PHASE(9);
   return sweeps;
 }
 

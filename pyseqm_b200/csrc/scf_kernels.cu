@@ -256,7 +256,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     SEQM_CUDA(cudaMemsetAsync(wk.stat, 0, 16, st));
     rc = launch_scf_small(t, w, M, g_ss, g_pp, g_sp, g_p2, h_sp, nheavy, nhydro, nocc, mp_small, opt->converger,
                           opt->alpha, opt->eps, max_iter_s, eigh_tolerance(), P, F, Eelec, nc, niter, pairvec, wk.Pold,
-                          wk.FOCK, wk.FPPF, wk.EMAT, wk.Vstore, wk.stat, wk.mol_atom0, wk.nn, st);
+                          wk.Pnew, wk.FOCK, wk.FPPF, wk.EMAT, wk.Vstore, wk.stat, wk.mol_atom0, wk.nn, st);
     if (rc) return rc;
     unsigned long long hs[2] = {0, 0};
     SEQM_CUDA(cudaMemcpyAsync(hs, wk.stat, 16, cudaMemcpyDeviceToHost, st));

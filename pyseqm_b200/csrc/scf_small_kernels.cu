@@ -6,6 +6,18 @@
 // involved between iterations and nothing but the Pulay ring, the previous density and the eigenvector store
 // (all L2 resident) goes to global memory.
 // reference: seqm/seqm_functions/scf_loop.py:32-510, fock.py:6-139, energy.py:19-36, diag.py:102-172
+#ifdef SEQM_SCF_TIMING
+__device__ long long g_phase_acc[16];
+__device__ long long g_phase_last;
+#define SEQM_PHASE(i)                                                              \
+  do {                                                                             \
+    if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) {                              \
+      const long long now_ = clock64();                                            \
+      g_phase_acc[(i)] += now_ - g_phase_last;                                     \
+      g_phase_last = now_;                                                         \
+    }                                                                              \
+  } while (0)
+#endif
 #include "eigh_warp.cuh"
 #include "dgemm.cuh"
 
@@ -27,7 +39,7 @@ struct SmallScfArgs {
   double *P, *F, *E;             // P in/out (padded), F out (padded, zero filled by the caller), E out
   uint8_t* nc;
   int32_t* niter;
-  double *pairvec, *Pold, *FOCK, *FPPF, *EMAT, *Vstore;
+  double *pairvec, *Pold, *Hpk, *FOCK, *FPPF, *EMAT, *Vstore;   // Hpk: packed core Hamiltonian scratch [B][nn]
   unsigned long long* stat;      // [0] molecules left unconverged, [1] largest iteration count
   size_t nn;                     // doubles per molecule in Pold / one ring slot
   int converger, max_iter;
@@ -162,37 +174,54 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   double* EMAT = A.EMAT ? A.EMAT + (size_t)mol * 36 : nullptr;
   double* Vg = A.Vstore + (size_t)mol * WV_LD * WV_LD;
 
+#ifdef SEQM_SCF_TIMING
+  if (blockIdx.x == 0 && lane == 0) g_phase_last = clock64();
+#endif
   build_schedule<N>(TAB, lane);
   // ---- P0 -> packed
   for (int idx = lane; idx < N * LD; idx += 32) {
     const int i = idx / LD, j = idx - i * LD;
     Ps[idx] = (i < m && j < m) ? A.P[base + (size_t)pk2pd(i, nh4) * n4 + pk2pd(j, nh4)] : 0.0;
   }
+  // packed, symmetrised core Hamiltonian of this molecule (hcore.py:73-158 stores the upper blocks only) -> Hpk
+  double* Hpk = A.Hpk + (size_t)mol * A.nn;
+  for (int idx = lane; idx < N * N; idx += 32) {
+    const int i = idx / N, j = idx - i * N;
+    double h = 0.0;
+    if (i < m && j < m) {
+      const int ai = i < nh4 ? i >> 2 : nh + i - nh4, mu = i < nh4 ? i & 3 : 0;
+      const int aj = j < nh4 ? j >> 2 : nh + j - nh4, nu = j < nh4 ? j & 3 : 0;
+      if (ai < aj || (ai == aj && mu <= nu)) h = A.M[(((size_t)mol * S + ai) * S + aj) * 16 + mu * 4 + nu];
+      else h = A.M[(((size_t)mol * S + aj) * S + ai) * 16 + nu * 4 + mu];
+    }
+    Hpk[idx] = h;
+  }
+  for (int idx = lane; idx < N * LD; idx += 32) { S0[idx] = 0.0; S1[idx] = 0.0; }
   if (EMAT && lane == 0) {
     for (int i = 0; i < 6; ++i)
       for (int j = 0; j < 6; ++j) EMAT[i * 6 + j] = (i > j) ? -1.0 : 0.0;
   }
   __syncwarp();
 
+  SEQM_PHASE(0);
   // F(Ps) -> S0, core Hamiltonian -> S1; returns 0.5 sum P (H + F)
   auto fock = [&]() -> double {
-    for (int idx = lane; idx < N * LD; idx += 32) {
-      const int i = idx / LD, j = idx - i * LD;
-      double h = 0.0;
-      if (i < m && j < m) {
-        const int ai = i < nh4 ? i >> 2 : nh + i - nh4, mu = i < nh4 ? i & 3 : 0;
-        const int aj = j < nh4 ? j >> 2 : nh + j - nh4, nu = j < nh4 ? j & 3 : 0;
-        if (ai < aj || (ai == aj && mu <= nu)) h = A.M[(((size_t)mol * S + ai) * S + aj) * 16 + mu * 4 + nu];
-        else h = A.M[(((size_t)mol * S + aj) * S + ai) * 16 + nu * 4 + mu];
+    SEQM_PHASE(11);
+#pragma unroll 4
+    for (int i = 0; i < N; ++i) {
+      if (lane < N) {
+        const double h = Hpk[i * N + lane];
+        S1[i * LD + lane] = h;
+        S0[i * LD + lane] = h;
       }
-      S1[idx] = h;
-      S0[idx] = h;
     }
     __syncwarp();
+    SEQM_PHASE(1);
     for (int s = lane; s < cls_n[2]; s += 32) small_fock_pair<SEQM_CLS_XX, LD>(A, mol, cls_lo[2] + s, nh, nh4, Ps, S0);
     for (int s = lane; s < cls_n[1]; s += 32) small_fock_pair<SEQM_CLS_XH, LD>(A, mol, cls_lo[1] + s, nh, nh4, Ps, S0);
     for (int s = lane; s < cls_n[0]; s += 32) small_fock_pair<SEQM_CLS_HH, LD>(A, mol, cls_lo[0] + s, nh, nh4, Ps, S0);
     __syncwarp();
+    SEQM_PHASE(2);
     // diagonal blocks: one-centre terms + the Coulomb vectors of the atom's pairs in pair order
     for (int q = lane; q < nat; q += 32) {
       const int a = atom0 + q;
@@ -202,6 +231,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
       double acc[10];
 #pragma unroll
       for (int k = 0; k < 10; ++k) acc[k] = 0.0;
+#pragma unroll 4
       for (int r = t.start_i[a]; r < t.start_i[a + 1]; ++r) {
         const double* pv = A.pairvec + (size_t)r * 20;
         acc[0] += pv[0];
@@ -210,6 +240,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
           for (int k = 1; k < 10; ++k) acc[k] += pv[k];
         }
       }
+#pragma unroll 4
       for (int r = t.start_j[a]; r < t.start_j[a + 1]; ++r) {
         const double* pv = A.pairvec + (size_t)t.perm_j[r] * 20 + 10;
         acc[0] += pv[0];
@@ -243,12 +274,15 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
       }
     }
     __syncwarp();
+    SEQM_PHASE(3);
     double e = 0.0;
     for (int idx = lane; idx < m * m; idx += 32) {
       const int i = idx / m, j = idx - i * m;
       e += 0.5 * Ps[i * LD + j] * (S1[i * LD + j] + S0[i * LD + j]);
     }
-    return warp_sum(e);
+    e = warp_sum(e);
+    SEQM_PHASE(4);
+    return e;
   };
 
   // P = mix(Pnew = S1, P = Ps, Pold)
@@ -330,45 +364,70 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
 
   // F = sum_s coeff_s FOCK[s] with the DIIS coefficients of the reference (scf_loop.py:471-496) -> S0
   auto pulay_extrapolate = [&](int c, int cF) {
-    double x[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    if (lane == 0) {
-      const int d = cF + 1;
-      double a[6][7];
-      for (int i = 0; i < 6; ++i)
-        for (int j = 0; j < 6; ++j) a[i][j] = EMAT[i * 6 + j] + (j > i ? EMAT[j * 6 + i] : 0.0);
-      const double sc = a[c][c];
-      for (int i = 0; i < cF; ++i)
-        for (int j = 0; j < cF; ++j) a[i][j] = a[i][j] / sc;
-      for (int i = 0; i < d; ++i) a[i][6] = (i == d - 1) ? 1.0 : 0.0;
-      for (int cc = 0; cc < d; ++cc) {
-        int piv = cc;
-        double best = fabs(a[cc][cc]);
-        for (int r = cc + 1; r < d; ++r)
-          if (fabs(a[r][cc]) > best) { best = fabs(a[r][cc]); piv = r; }
-        if (piv != cc) {
-          for (int j = 0; j < 7; ++j) { const double tmp = a[cc][j]; a[cc][j] = a[piv][j]; a[piv][j] = tmp; }
+    // EVEC = EMAT + tril(EMAT,-1)^T, EVEC[:cF,:cF] /= EVEC[c][c], solve EVEC[:d,:d] x = e_{d-1} (d = cF + 1) by
+    // Gaussian elimination with partial pivoting: lane i holds row i (7 values, static column indices), rows are
+    // exchanged and broadcast with shuffles; the arithmetic and its order are those of the serial elimination
+    const int d = cF + 1;
+    const int row = lane < 6 ? lane : 5;
+    double r[7];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) r[j] = EMAT[row * 6 + j] + (j > row ? EMAT[j * 6 + row] : 0.0);
+    {
+      const double sc = EMAT[c * 6 + c];
+#pragma unroll
+      for (int j = 0; j < 6; ++j)
+        if (row < cF && j < cF) r[j] = r[j] / sc;
+    }
+    r[6] = (lane == d - 1) ? 1.0 : 0.0;
+#pragma unroll
+    for (int cc = 0; cc < 6; ++cc) {
+      if (cc < d) {
+        double best = (lane >= cc && lane < d) ? fabs(r[cc]) : -1.0;
+        int piv = lane;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(FULL, best, o);
+          const int op = __shfl_xor_sync(FULL, piv, o);
+          if (ob > best || (ob == best && op < piv)) { best = ob; piv = op; }
         }
-        const double inv = 1.0 / a[cc][cc];
-        for (int r = cc + 1; r < d; ++r) {
-          const double f = a[r][cc] * inv;
-          for (int j = cc; j < d; ++j) a[r][j] -= f * a[cc][j];
-          a[r][6] -= f * a[cc][6];
+        piv = __shfl_sync(FULL, piv, 0);
+        const int src = lane == cc ? piv : (lane == piv ? cc : lane);
+        double pr[7];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) {
+          r[j] = __shfl_sync(FULL, r[j], src);
+          pr[j] = __shfl_sync(FULL, r[j], cc);
         }
+        const double inv = 1.0 / pr[cc];
+        const double f = (lane > cc && lane < d) ? r[cc] * inv : 0.0;
+#pragma unroll
+        for (int j = 0; j < 7; ++j)
+          if (j >= cc) r[j] -= f * pr[j];
       }
-      for (int r = d - 1; r >= 0; --r) {
-        double sum = a[r][6];
-        for (int j = r + 1; j < d; ++j) sum -= a[r][j] * x[j];
-        x[r] = sum / a[r][r];
+    }
+    double x[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int rr = 5; rr >= 0; --rr) {
+      if (rr < d) {
+        double sum = r[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+          if (j > rr && j < d) sum -= r[j] * x[j];
+        x[rr] = __shfl_sync(FULL, sum / r[rr], rr);
       }
     }
     double coeff[SNFOCK];
 #pragma unroll
-    for (int s = 0; s < SNFOCK; ++s) coeff[s] = -__shfl_sync(FULL, x[s], 0);
-    for (int idx = lane; idx < N * N; idx += 32) {
-      const int i = idx / N, j = idx - i * N;
-      double acc = 0.0;
-      for (int s = 0; s < cF; ++s) acc += FOCK[(size_t)s * A.nn + idx] * coeff[s];
-      S0[i * LD + j] = acc;
+    for (int s = 0; s < SNFOCK; ++s) coeff[s] = -x[s];
+#pragma unroll 3
+    for (int i = 0; i < N; ++i) {
+      if (lane < N) {
+        double acc = 0.0;
+#pragma unroll
+        for (int s = 0; s < SNFOCK; ++s)
+          if (s < cF) acc += FOCK[(size_t)s * A.nn + i * N + lane] * coeff[s];
+        S0[i * LD + lane] = acc;
+      }
     }
     __syncwarp();
   };
@@ -390,6 +449,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
         cF = cF < SNFOCK ? cF + 1 : SNFOCK;
         counter = (counter + 1) % SNFOCK;
         pulay_store(counter, cF);
+        SEQM_PHASE(5);
       }
       const double err = fabs(en - E);
       E = en;
@@ -404,8 +464,10 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     else if (A.converger == 1 || k == 2) mode = SMIX_ADAPTIVE;
     else mode = SMIX_TAKE;
     if (A.converger == 2 && k >= 5) pulay_extrapolate(counter, cF);
+    SEQM_PHASE(6);
     warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr);
     mix(mode);
+    SEQM_PHASE(10);
   }
 
   // ---- results back to the padded layout
@@ -444,7 +506,7 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
                      const double* g_sp, const double* g_p2, const double* h_sp, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, int mp, int converger, double alpha, double eps,
                      int max_iter, double tol, double* P, double* F, double* E, uint8_t* nc, int32_t* niter,
-                     double* pairvec, double* Pold, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
+                     double* pairvec, double* Pold, double* Hpk, double* FOCK, double* FPPF, double* EMAT, double* Vstore,
                      unsigned long long* stat, int32_t* mol_atom0, size_t nn, cudaStream_t st) {
   prof_mark("scf_small", st);
   mol_atom0_kernel<<<cdiv(t.natoms > 0 ? t.natoms : 1, 256), 256, 0, st>>>((int)t.natoms, (int)t.nmol, t.atom_mol, mol_atom0);
@@ -452,7 +514,7 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
   SmallScfArgs a{};
   a.t = t; a.w = w; a.M = M; a.gss = g_ss; a.gpp = g_pp; a.gsp = g_sp; a.gp2 = g_p2; a.hsp = h_sp;
   a.nheavy = nheavy; a.nhydro = nhydro; a.nocc = nocc; a.mol_atom0 = mol_atom0;
-  a.P = P; a.F = F; a.E = E; a.nc = nc; a.niter = niter; a.pairvec = pairvec; a.Pold = Pold; a.FOCK = FOCK;
+  a.P = P; a.F = F; a.E = E; a.nc = nc; a.niter = niter; a.pairvec = pairvec; a.Pold = Pold; a.Hpk = Hpk; a.FOCK = FOCK;
   a.FPPF = FPPF; a.EMAT = EMAT; a.Vstore = Vstore; a.stat = stat; a.nn = nn; a.converger = converger;
   a.max_iter = max_iter; a.alpha = alpha; a.eps = eps; a.tol = tol;
   int rc;
@@ -468,5 +530,17 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
 #undef SEQM_SMALL_CASE
   return fail(SEQM_EUNSUPPORTED, "launch_scf_small: packed size above 32");
 }
+
+#ifdef SEQM_SCF_TIMING
+}  // namespace seqm
+extern "C" int seqm_debug_phase_ticks(long long* out, int reset) {
+  long long z[16] = {0};
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_phase_acc, sizeof(z));
+  if (reset) cudaMemcpyToSymbol(g_phase_acc, z, sizeof(z));
+  return 0;
+}
+namespace seqm {
+#endif
 
 }  // namespace seqm
