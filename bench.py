@@ -406,15 +406,47 @@ def run_c60xl(args, rank, world, local_rank):
     tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
     for v in prof.values():
         v["share"] = v["ms"] / tot_prof
+    # FP64 GEMM peak of this box, measured here (cuBLAS DGEMM through torch.matmul, 4096^3, best of 5): denominator
+    A_ = torch.randn(4096, 4096, device=dev)
+    B_ = torch.randn(4096, 4096, device=dev)
+    torch.matmul(A_, B_)
+    best = 1e30
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(A_, B_)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    fp64_peak = 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
+    del A_, B_
     m = 240
-    dg = prof.get('dgemm', {"ms": 0.0, "launch_groups": 1, "share": 0.0})
-    flops = 2.0 * m ** 3 * nmol
-    per_launch = dg["ms"] / max(dg["launch_groups"], 1)
-    roof = {"bound": "tensor", "kernel": "dgemm_batched (SP2, DMMA m8n8k4 f64)", "share_of_step": dg["share"],
-            "achieved": flops / (per_launch * 1e-3) / 1e12 if per_launch else None, "peak": 40.0,
-            "peak_source": "B200 FP64 datasheet figure (MEASURED_PEAKS.json holds no FP64 number)", "unit": "TFLOP/s",
-            "frac": flops / (per_launch * 1e-3) / 1e12 / 40.0 if per_launch else None, "traffic": None,
-            "note": "all molecules counted live in every SP2 product (upper bound on work per launch)"}
+    sp = prof.get('sp2_step', {"ms": 0.0, "launch_groups": 1, "share": 0.0})
+    nstep_launch = 2 * max(sp["launch_groups"], 1)          # two purification steps per profiled group
+    flops = 2.0 * m ** 3 * nmol                              # 2 m^3 per multiplication and molecule
+    per_launch = sp["ms"] / nstep_launch
+    T_ = (m + 63) // 64
+    roof = {"bound": "tensor", "kernel": "sp2_step_kernel (X^2 on the upper block triangle, DMMA m8n8k4 f64, fused trace "
+                                         "rule / update / transpose epilogue)", "share_of_step": sp["share"],
+            "achieved": flops / (per_launch * 1e-3) / 1e12 if per_launch else None, "peak": fp64_peak,
+            "peak_source": "cuBLAS DGEMM 4096^3 measured in this run (MEASURED_PEAKS.json holds no FP64 number)",
+            "unit": "TFLOP/s", "frac": flops / (per_launch * 1e-3) / 1e12 / fp64_peak if per_launch else None,
+            "traffic": None,
+            "note": "algorithmic flops 2 m^3 per product; the kernel executes %d of %d tiles (symmetry), i.e. %.3f of "
+                    "them; the last launch of the loop may be a no-op" % (T_ * (T_ + 1) // 2, T_ * T_,
+                                                                        (T_ + 1) / (2.0 * T_))}
+    # HBM fraction of the integral / Fock kernels at this size (one launch each inside the profiled step)
+    hbm, peak_src = peaks()
+    npair = nmol * 60 * 59 // 2
+    kb = {'pair_fwd': npair * (48 + 800 + 128 + 8 + 160) + nmol * 60 * 224,
+          'fock_pair': npair * (800 + 4 * 128 + 160 + 16),
+          'pair_grad': npair * (48 + 3 * 128 + 32) + nmol * 60 * 224}
+    kernels = {}
+    for nm_, nbytes in kb.items():
+        if nm_ in prof and prof[nm_]["ms"] > 0:
+            ms_ = prof[nm_]["ms"] / max(prof[nm_]["launch_groups"], 1)
+            kernels[nm_] = {"ms_per_launch": ms_, "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / (ms_ * 1e-3) / 1e9,
+                            "frac_of_hbm": nbytes / (ms_ * 1e-3) / 1e9 / hbm}
     ms_step = total_ms / args.steps
     print(json.dumps({
         "metric": "XL-BOMD steps/sec", "value": world / (ms_step * 1e-3), "unit": "batch steps/s", "n_gpus": world,
@@ -427,8 +459,8 @@ def run_c60xl(args, rank, world, local_rank):
                 "d2h_bytes_per_step": nmol * 60 * 3 * 8 + nmol * 8,
                 "note": "MD state lives on the device (as in the reference); coordinates and Hf go to pinned host "
                         "memory every step"},
-        "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
-        "cpu_baseline": None}))
+        "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
+        "profile_one_step": prof, "cpu_baseline": None}))
     if world > 1:
         dist.destroy_process_group()
 

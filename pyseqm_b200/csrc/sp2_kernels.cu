@@ -86,77 +86,223 @@ sp2_init_kernel(int S, int ld, const double* __restrict__ F, const int32_t* __re
   }
 }
 
-// after X2 = X X: trace rule, new trace from the diagonals the update will produce, convergence flags
+// ---------------------------------------------------------------------------------------------
+// Fused SP2 step: one launch per purification step.
+//   prologue   every CTA of molecule b sums the (fixed-order) partial traces the previous step left behind:
+//              t1 = tr X, t2 = |X|_F^2 = tr X^2 (X symmetric), takes the branch of the trace rule and the
+//              convergence decision -- all CTAs of a molecule compute the same scalars from the same numbers
+//   main loop  Y = X X for one 64x64 tile of the UPPER block triangle (DMMA m8n8k4, cp.async double buffering)
+//   epilogue   Xnew = Y or 2X - Y, staged through shared memory and written to the other buffer as the tile and
+//              its transpose (coalesced both ways); partial sums of diag(Xnew) and |Xnew|_F^2 for the next step
+// Per-molecule scalars are double buffered by step parity (tile 0 writes, everybody reads the other copy).
+// ---------------------------------------------------------------------------------------------
+constexpr int SBM = 64, SBK = 16;
+constexpr int SLDA = SBK + 4, SLDB = SBM + 4, SLDT = SBM + 1;
+
+struct Sp2Step {       // per molecule and parity
+  double e0, e1;       // |tr X - nocc| after the last two steps
+  int live, niter, buf, pad;
+};
+
+__device__ __forceinline__ void s_cp_async16(void* smem, const void* gmem, bool pred) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  const int bytes = pred ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(sa), "l"(gmem), "r"(bytes));
+}
+__device__ __forceinline__ void s_dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
 __global__ void __launch_bounds__(256)
-sp2_decide_kernel(int ld, double eps, const int32_t* __restrict__ dims, const double* __restrict__ X,
-                  const double* __restrict__ X2, Sp2State* __restrict__ st, uint8_t* __restrict__ live,
-                  int* __restrict__ nlive) {
-  const int mol = blockIdx.x;
-  if (!live[mol]) return;
-  __shared__ double red[8];
-  const int m = dims[mol];
-  const double* Xm = X + (size_t)mol * ld * ld;
-  const double* Ym = X2 + (size_t)mol * ld * ld;
+sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int32_t* __restrict__ dims,
+                const double* __restrict__ occ, double* __restrict__ Xbuf0, double* __restrict__ Xbuf1,
+                long long stride, Sp2Step* __restrict__ state, double* __restrict__ partial, int* __restrict__ nlive) {
+  const int b = b0 + blockIdx.y;
+  const Sp2Step sin = state[(size_t)(step & 1) * nmol + b];
+  if (!sin.live) {      // keep both parities of a finished molecule identical
+    if (blockIdx.x == 0 && threadIdx.x == 0) state[(size_t)((step + 1) & 1) * nmol + b] = sin;
+    return;
+  }
+  const int nn = dims[b];
+  const int TT = (nn + SBM - 1) / SBM;                      // tile rows of this molecule
+  // tile id -> (ti <= tj) in the batch-wide enumeration of the upper block triangle of a T x T grid
+  int ti = 0, rem = blockIdx.x;
+  while (rem >= T - ti) { rem -= T - ti; ++ti; }
+  const int tj = ti + rem;
+  const int ntile = T * (T + 1) / 2;
+  const double* pin = partial + ((size_t)(step & 1) * nmol + b) * 2 * ntile;
+  double* pout = partial + ((size_t)((step + 1) & 1) * nmol + b) * 2 * ntile;
   double t1 = 0.0, t2 = 0.0;
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
-    t1 += Xm[(size_t)i * ld + i];
-    t2 += Ym[(size_t)i * ld + i];
+  for (int q = 0; q < ntile; ++q) { t1 += pin[2 * q]; t2 += pin[2 * q + 1]; }
+  const double oc = occ[b];
+  const bool square = fabs(t2 - oc) < fabs(2.0 * t1 - t2 - oc);
+  const double tn = square ? t2 : 2.0 * t1 - t2;
+  const int tid = threadIdx.x;
+  if (blockIdx.x == 0 && tid == 0) {
+    Sp2Step so;
+    so.e1 = sin.e0;
+    so.e0 = fabs(tn - oc);
+    so.niter = sin.niter + 1;
+    so.buf = (sin.buf ^ 1);
+    so.live = ((so.e0 < eps) && (so.e1 < eps)) ? 0 : 1;
+    so.pad = 0;
+    state[(size_t)((step + 1) & 1) * nmol + b] = so;
+    if (so.live) atomicAdd(nlive, 1);
   }
-  t1 = blk_reduce(t1, red, 0);
-  t2 = blk_reduce(t2, red, 0);
-  const double occ = st[mol].occ;
-  const bool square = fabs(t2 - occ) < fabs(2.0 * t1 - t2 - occ);
-  double tn = 0.0;
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
-    const double x = Xm[(size_t)i * ld + i], y = Ym[(size_t)i * ld + i];
-    tn += square ? y : 2.0 * x - y;
+  if (ti >= TT || tj >= TT) {           // tile outside this (smaller) molecule: contributes nothing
+    if (tid == 0) { pout[2 * blockIdx.x] = 0.0; pout[2 * blockIdx.x + 1] = 0.0; }
+    return;
   }
-  tn = blk_reduce(tn, red, 0);
+  const double* Xin = (sin.buf ? Xbuf1 : Xbuf0) + (size_t)b * stride;
+  double* Xout = (sin.buf ? Xbuf0 : Xbuf1) + (size_t)b * stride;
+  const int m0 = ti * SBM, n0 = tj * SBM;
+  __shared__ __align__(16) double sm[2 * SBM * SLDA + 2 * SBK * SLDB];
+  double* As0 = sm;
+  double* Bs0 = sm + 2 * SBM * SLDA;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int wm = (warp >> 1) * 16, wn = (warp & 1) * 32;
+  const int g = lane >> 2, t = lane & 3;
+  double acc[2][4][2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+  auto load_tiles = [&](int buf, int k0) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int idx = tid + it * 256;
+      const int r = idx >> 3, c2 = (idx & 7) * 2;
+      const int gr = m0 + r, gc = k0 + c2;
+      const bool ok = gr < nn && gc < nn;
+      s_cp_async16(&As0[buf * SBM * SLDA + r * SLDA + c2], Xin + (size_t)(ok ? gr : 0) * ld + (ok ? gc : 0), ok);
+    }
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int idx = tid + it * 256;
+      const int r = idx >> 5, c2 = (idx & 31) * 2;
+      const int gr = k0 + r, gc = n0 + c2;
+      const bool ok = gr < nn && gc < nn;
+      s_cp_async16(&Bs0[buf * SBK * SLDB + r * SLDB + c2], Xin + (size_t)(ok ? gr : 0) * ld + (ok ? gc : 0), ok);
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+  const int nk = (nn + SBK - 1) / SBK;
+  load_tiles(0, 0);
+  for (int kt = 0; kt < nk; ++kt) {
+    const int buf = kt & 1;
+    if (kt + 1 < nk) {
+      load_tiles(buf ^ 1, (kt + 1) * SBK);
+      asm volatile("cp.async.wait_group 1;\n" ::);
+    } else {
+      asm volatile("cp.async.wait_group 0;\n" ::);
+    }
+    __syncthreads();
+    const double* as = As0 + buf * SBM * SLDA;
+    const double* bs = Bs0 + buf * SBK * SLDB;
+#pragma unroll
+    for (int kk = 0; kk < SBK; kk += 4) {
+      double af[2], bf[4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) af[i] = as[(wm + i * 8 + g) * SLDA + kk + t];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bf[j] = bs[(kk + t) * SLDB + wn + j * 8 + g];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+    __syncthreads();
+  }
+  // ---- epilogue: Xnew tile into shared memory (the staging buffers are free now)
+  double* Ts = sm;                      // [64][65]
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int rl = wm + i * 8 + g;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int cl = wn + j * 8 + 2 * t;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int r = m0 + rl, c = n0 + cl + h;
+        double y = acc[i][j][h];
+        if (r < nn && c < nn) {
+          if (!square) y = 2.0 * Xin[(size_t)r * ld + c] - y;
+        } else {
+          y = 0.0;
+        }
+        Ts[rl * SLDT + cl + h] = y;
+      }
+    }
+  }
+  __syncthreads();
+  double ptr = 0.0, pfr = 0.0;
+  for (int idx = tid; idx < SBM * SBM; idx += 256) {
+    const int rl = idx >> 6, cl = idx & 63;
+    const int r = m0 + rl, c = n0 + cl;
+    if (r < nn && c < nn) {
+      const double y = Ts[rl * SLDT + cl];
+      Xout[(size_t)r * ld + c] = y;
+      pfr += y * y;
+      if (ti == tj && rl == cl) ptr += y;
+    }
+    if (ti != tj) {                     // transposed tile: row n0 + rl, column m0 + cl
+      const int r2 = n0 + rl, c2 = m0 + cl;
+      if (r2 < nn && c2 < nn) Xout[(size_t)r2 * ld + c2] = Ts[cl * SLDT + rl];
+    }
+  }
+  if (ti != tj) pfr *= 2.0;
+  __shared__ double red[8];
+  ptr = blk_reduce(ptr, red, 0);
+  pfr = blk_reduce(pfr, red, 0);
+  if (tid == 0) { pout[2 * blockIdx.x] = ptr; pout[2 * blockIdx.x + 1] = pfr; }
+}
+
+// initial per-molecule scalars of the fused loop from the state sp2_init_kernel produced (X0 in buffer 0)
+__global__ void sp2_step_init_kernel(int nmol, int ntile, int ld, const int32_t* __restrict__ dims,
+                                     const Sp2State* __restrict__ st, const double* __restrict__ X, long long stride,
+                                     Sp2Step* __restrict__ state, double* __restrict__ partial, double* __restrict__ occ) {
+  const int b = blockIdx.x;
+  __shared__ double red[8];
+  const int m = dims[b];
+  const bool live = st[b].live != 0;
+  double fr = 0.0;
+  if (live) {
+    const double* Xm = X + (size_t)b * stride;
+    for (int idx = threadIdx.x; idx < m * m; idx += blockDim.x) {
+      const int i = idx / m, j = idx - i * m;
+      const double x = Xm[(size_t)i * ld + j];
+      fr += x * x;
+    }
+  }
+  fr = blk_reduce(fr, red, 0);
   if (threadIdx.x == 0) {
-    Sp2State s = st[mol];
-    s.square = square ? 1 : 0;
-    s.e1 = s.e0;
-    s.e0 = fabs(tn - occ);
-    s.tr = tn;
-    s.niter += 1;
-    const bool done = (s.e0 < eps) && (s.e1 < eps);
-    s.live = done ? 0 : 1;
-    st[mol] = s;
-    if (!done) atomicAdd(nlive, 1);
+    Sp2Step s;
+    s.e0 = st[b].e0; s.e1 = st[b].e1; s.live = live ? 1 : 0; s.niter = 0; s.buf = 0; s.pad = 0;
+    state[b] = s;
+    s.live = 0;
+    state[(size_t)nmol + b] = s;
+    occ[b] = st[b].occ;
+    for (int q = 0; q < 2 * ntile; ++q) partial[(size_t)b * 2 * ntile + q] = 0.0;
+    partial[(size_t)b * 2 * ntile] = st[b].tr;
+    partial[(size_t)b * 2 * ntile + 1] = fr;
   }
 }
 
-// X = X2 or 2X - X2 for the molecules that took this step (live_prev), grid (chunks, nmol)
+// D = 2 X from the buffer each molecule finished in
 __global__ void __launch_bounds__(256)
-sp2_update_kernel(int ld, const uint8_t* __restrict__ took, const Sp2State* __restrict__ st,
-                  double* __restrict__ X, const double* __restrict__ X2) {
-  const int mol = blockIdx.y;
-  if (!took[mol]) return;
-  const bool square = st[mol].square != 0;
-  const size_t nn = (size_t)ld * ld;
-  double* Xm = X + (size_t)mol * nn;
-  const double* Ym = X2 + (size_t)mol * nn;
-  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < nn; idx += (size_t)gridDim.x * blockDim.x) {
-    const double y = Ym[idx];
-    Xm[idx] = square ? y : 2.0 * Xm[idx] - y;
-  }
-}
-
-__global__ void sp2_sync_live_kernel(int nmol, const Sp2State* __restrict__ st, uint8_t* __restrict__ live) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b < nmol) live[b] = st[b].live ? 1 : 0;
-}
-
-// D = 2 X, unpacked into the padded layout (pack.py:34-41)
-__global__ void __launch_bounds__(256)
-sp2_finish_kernel(int S, int ld, const double* __restrict__ X, const int32_t* __restrict__ nheavy,
-                  const int32_t* __restrict__ dims, const uint8_t* __restrict__ active, const Sp2State* __restrict__ st,
-                  double* __restrict__ D, int32_t* __restrict__ niter) {
-  const int mol = blockIdx.y;
+sp2_finish2_kernel(int S, int ld, const double* __restrict__ X0, const double* __restrict__ X1, long long stride,
+                   const int32_t* __restrict__ nheavy, const int32_t* __restrict__ dims,
+                   const uint8_t* __restrict__ active, const Sp2Step* __restrict__ sa, const Sp2Step* __restrict__ sb,
+                   int b0, double* __restrict__ D, int32_t* __restrict__ niter) {
+  const int mol = b0 + blockIdx.y;
   if (active && !active[mol]) return;
+  // the entry with the larger iteration count is the last one written for this molecule
+  const Sp2Step s = sa[mol].niter >= sb[mol].niter ? sa[mol] : sb[mol];
   const int m = dims[mol], nh4 = 4 * nheavy[mol], n4 = 4 * S;
-  if (niter && blockIdx.x == 0 && threadIdx.x == 0) niter[mol] = st[mol].niter;
-  const double* Xm = X + (size_t)mol * ld * ld;
+  if (niter && blockIdx.x == 0 && threadIdx.x == 0) niter[mol] = s.niter;
+  const double* Xm = (s.buf ? X1 : X0) + (size_t)mol * stride;
   double* Dm = D + (size_t)mol * n4 * n4;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < m * m; idx += gridDim.x * blockDim.x) {
     const int i = idx / m, j = idx - i * m;
@@ -166,6 +312,7 @@ sp2_finish_kernel(int S, int ld, const double* __restrict__ X, const int32_t* __
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static int sp2_ld(int mmax) { return (mmax + 3) & ~3; }
+static int sp2_tiles(int ld) { const int T = (ld + SBM - 1) / SBM; return T * (T + 1) / 2; }
 
 }  // namespace seqm
 
@@ -175,7 +322,9 @@ extern "C" {
 
 size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize) {
   const size_t ld = (size_t)4 * molsize;       // upper bound of the packed size
-  return 2 * al256((size_t)nmol * ld * ld * 8) + al256(nmol * sizeof(Sp2State)) + al256(nmol * 4) + 2 * al256(nmol) + 256;
+  const size_t ntile = (size_t)sp2_tiles((int)ld);
+  return 2 * al256((size_t)nmol * ld * ld * 8) + al256(nmol * sizeof(Sp2State)) + al256(nmol * 4) +
+         al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + al256(nmol * 8) + 256;
 }
 
 int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
@@ -189,47 +338,58 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   if (eps > 1.0e-3) eps = 1.0e-3;
   const int B = (int)nmol, S = (int)molsize, ld = sp2_ld(mmax);
   const size_t ldmax = (size_t)4 * molsize;
+  const int T = (ld + SBM - 1) / SBM, ntile = T * (T + 1) / 2;
   char* base = (char*)work;
-  double* X = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
-  double* X2 = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
-  Sp2State* state = (Sp2State*)base; base += al256(nmol * sizeof(Sp2State));
+  double* X0 = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
+  double* X1 = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
+  Sp2State* init = (Sp2State*)base; base += al256(nmol * sizeof(Sp2State));
   int32_t* dims = (int32_t*)base; base += al256(nmol * 4);
-  uint8_t* live = (uint8_t*)base; base += al256(nmol);
-  uint8_t* took = (uint8_t*)base; base += al256(nmol);
-  int* nlive = (int*)base;
-  prof_mark("sp2_init", st);
-  sp2_init_kernel<<<B, 256, 0, st>>>(S, ld, F, nheavy, nhydro, nocc, active, X, state, dims);
-  SEQM_CHECK_LAUNCH("sp2_init_kernel");
-  sp2_sync_live_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, state, live);
-  SEQM_CHECK_LAUNCH("sp2_sync_live_kernel");
+  Sp2Step* state = (Sp2Step*)base; base += al256(2 * nmol * sizeof(Sp2Step));
+  double* partial = (double*)base; base += al256((size_t)2 * nmol * 2 * sp2_tiles((int)ldmax) * 8);
+  double* occ = (double*)base; base += al256(nmol * 8);
+  int* nlive = (int*)base;       // [2]
   const long long stride = (long long)ld * ld;
-  int chunks = (int)((stride + 256 * 8 - 1) / (256 * 8));
-  if (chunks > 1024) chunks = 1024;
-  if (chunks < 1) chunks = 1;
+  prof_mark("sp2_init", st);
+  sp2_init_kernel<<<B, 256, 0, st>>>(S, ld, F, nheavy, nhydro, nocc, active, X0, init, dims);
+  SEQM_CHECK_LAUNCH("sp2_init_kernel");
+  sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, ld, dims, init, X0, stride, state, partial, occ);
+  SEQM_CHECK_LAUNCH("sp2_step_init_kernel");
   int* hlive = nullptr;
-  SEQM_CUDA(cudaMallocHost(&hlive, sizeof(int)));
+  SEQM_CUDA(cudaMallocHost(&hlive, 2 * sizeof(int)));
   int rc = SEQM_OK;
-  for (int it = 0; it < 200; ++it) {
-    rc = launch_dgemm_batched(ld, ld, X, X, X2, stride, B, live, dims, st);
+  // two purification steps per host synchronisation: the second is a no-op (CTAs exit on the live flag) when the
+  // first one finished every molecule
+  for (int it = 0; it < 200 && rc == SEQM_OK; it += 2) {
+    prof_mark("sp2_step", st);
+    cudaMemsetAsync(nlive, 0, 2 * sizeof(int), st);
+    for (int h = 0; h < 2; ++h) {
+      for (int b0 = 0; b0 < B; b0 += 65535) {
+        const int nb = B - b0 < 65535 ? B - b0 : 65535;
+        sp2_step_kernel<<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it + h, eps, dims, occ, X0, X1, stride, state,
+                                                        partial, nlive + h);
+        cudaError_t e_ = cudaGetLastError();
+        ++g_launches;
+        if (e_ != cudaSuccess) { set_error(std::string("sp2_step_kernel: ") + cudaGetErrorString(e_)); rc = SEQM_ECUDA; break; }
+      }
+      if (rc) break;
+    }
     if (rc) break;
-    prof_mark("sp2_update+host_sync", st);
-    cudaMemsetAsync(nlive, 0, sizeof(int), st);
-    cudaMemcpyAsync(took, live, B, cudaMemcpyDeviceToDevice, st);
-    sp2_decide_kernel<<<B, 256, 0, st>>>(ld, eps, dims, X, X2, state, live, nlive);
-    sp2_update_kernel<<<dim3(chunks, B), 256, 0, st>>>(ld, took, state, X, X2);
-    sp2_sync_live_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, state, live);
-    cudaMemcpyAsync(hlive, nlive, sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(hlive, nlive, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
     cudaError_t e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) { set_error(std::string("sp2 loop: ") + cudaGetErrorString(e)); rc = SEQM_ECUDA; break; }
-    if (*hlive == 0) break;
+    if (hlive[0] == 0 || hlive[1] == 0) break;
   }
   cudaFreeHost(hlive);
   if (rc) return rc;
   int fchunks = (int)(((long long)mmax * mmax + 255) / 256);
   if (fchunks > 512) fchunks = 512;
   prof_mark("sp2_finish", st);
-  sp2_finish_kernel<<<dim3(fchunks, B), 256, 0, st>>>(S, ld, X, nheavy, dims, active, state, D, niter);
-  SEQM_CHECK_LAUNCH("sp2_finish_kernel");
+  for (int b0 = 0; b0 < B; b0 += 65535) {
+    const int nb = B - b0 < 65535 ? B - b0 : 65535;
+    sp2_finish2_kernel<<<dim3(fchunks, nb), 256, 0, st>>>(S, ld, X0, X1, stride, nheavy, dims, active, state, state + B, b0,
+                                                          D, niter);
+    SEQM_CHECK_LAUNCH("sp2_finish2_kernel");
+  }
   prof_mark("end", st);
   return SEQM_OK;
 }
