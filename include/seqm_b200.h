@@ -167,6 +167,9 @@ typedef struct {
   double eps;         /* |dEelec| threshold, eV */
   int max_iter;
   int debug;          /* print "scf k max_err n_notconverged" like scf_loop.debug */
+  int async_status;   /* one-launch form only: do not synchronise; iterations_out then points to 16 bytes of
+                         page-locked host memory that receive two uint64 {molecules left, iterations run} when the
+                         stream reaches the end of the SCF */
 } seqm_scf_options_t;
 void seqm_scf_fused(int on);
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);

@@ -67,7 +67,7 @@ def _toc(const, key, t0):
 
 def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters, method,
           run_scf=True, P0=None, eps=1.0e-4, sp2=(False,), scf_converger=(1,), max_iter=1000, debug=False,
-          topo=None, atompar=None, P_guess=None):
+          topo=None, atompar=None, P_guess=None, defer_status=False):
     """-> state dict: topo, atompar, w, M, EnucAB, pv and (if run_scf) P, F, Eelec, notconverged, niter"""
     for k in ('Kbeta', 'g_ss_nuc'):
         if k in parameters:
@@ -92,13 +92,36 @@ def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij,
                 P = P_guess
             else:
                 P = initial_density(const, topo, Z, maskd)
-            P, F, E, nc, nit, (iters, left) = _ops.scf(topo, w, M, par5, P, float(eps), list(scf_converger), list(sp2),
-                                                       max_iter, debug, pv)
-        st.update(P=P, F=F, Eelec=E, notconverged=nc, niter=nit, iterations=iters)
-        if left:
-            warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (left, nmol, max_iter))
+            status = None
+            if defer_status and not const.do_timing:
+                status = torch.zeros(2, dtype=torch.int64).pin_memory()
+            P, F, E, nc, nit, done = _ops.scf(topo, w, M, par5, P, float(eps), list(scf_converger), list(sp2), max_iter,
+                                              debug, pv, status=status)
+        st.update(P=P, F=F, Eelec=E, notconverged=nc, niter=nit, nmol=int(nmol), max_iter=max_iter)
+        if done is None:
+            st['status'] = status          # resolved by resolve_status() once the stream has been synchronised
+            st['iterations'] = None
+        else:
+            st['iterations'] = done[0]
+            _warn_unconverged(done[1], nmol, max_iter)
         _toc(const, "SCF", t0)
     return st
+
+
+def _warn_unconverged(left, nmol, max_iter):
+    if left:
+        warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (left, nmol, max_iter))
+
+
+def resolve_status(st):
+    """finish a build() made with defer_status: wait for the stream, read {left, iterations}, warn like the reference"""
+    status = st.pop('status', None)
+    if status is None:
+        return
+    torch.cuda.current_stream().synchronize()
+    left, iters = int(status[0]), int(status[1])
+    st['iterations'] = iters
+    _warn_unconverged(left, st['nmol'], st['max_iter'])
 
 
 def hcore_matrix(M, nmol, molsize):

@@ -27,7 +27,7 @@ class WStore(ctypes.Structure):
 class ScfOptions(ctypes.Structure):
     _fields_ = [('converger', ctypes.c_int), ('alpha', ctypes.c_double), ('use_sp2', ctypes.c_int),
                 ('sp2_eps', ctypes.c_double), ('eps', ctypes.c_double), ('max_iter', ctypes.c_int),
-                ('debug', ctypes.c_int)]
+                ('debug', ctypes.c_int), ('async_status', ctypes.c_int)]
 
 
 class SeqmError(RuntimeError):
@@ -73,7 +73,7 @@ def lib():
         L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
         L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
         L.seqm_scf.argtypes = [TP, WStore] + [VP] * 9 + [ci, ctypes.POINTER(ScfOptions)] + [VP] * 7 + \
-                              [ctypes.POINTER(ctypes.c_int32), VP]
+                              [VP, VP]
         L.seqm_pair_grad.argtypes = [TP, VP, VP, VP, ci] + [VP] * 7
         L.seqm_dgemm_batched.argtypes = [i64, i64, VP, VP, VP, i64, i64, VP, VP]
         L.seqm_pair_geometry.argtypes = [TP, VP, cd, VP, VP, VP]

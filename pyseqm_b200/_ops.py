@@ -122,8 +122,15 @@ def sp2_density(F, nheavy, nhydro, nocc, molsize, mmax, eps, active=None, want_n
     return (D, nit) if want_niter else D
 
 
-def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv):
-    """-> P, F, Eelec, notconverged(bool), niter[B], iterations"""
+def scf_is_fused(topo, sp2, debug):
+    """the one-launch form of seqm_scf applies (include/seqm_b200.h)"""
+    return (not sp2[0]) and (not debug) and ((max(int(topo.mmax), 1) + 1) & ~1) <= 32
+
+
+def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv, status=None):
+    """-> P, F, Eelec, notconverged(bool), niter[B], (iterations, left).
+    status: pinned int64[2] tensor -> no synchronisation (one-launch form only); the last element is then None and
+    status receives {left, iterations} when the stream gets there (see ScfStatus)."""
     dev = topo.device
     B, S = topo.nmol, topo.molsize
     n4 = 4 * S
@@ -137,6 +144,8 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv):
     opt.debug = 1 if debug else 0
     if opt.converger not in (0, 1, 2):
         raise ValueError("scf_converger should be [0, alpha], [1] or [2]")
+    use_async = status is not None and scf_is_fused(topo, sp2, debug)
+    opt.async_status = 1 if use_async else 0
     P = _f64(P0).clone()
     F = torch.empty(B, n4, n4, dtype=torch.float64, device=dev)
     E = torch.zeros(B, dtype=torch.float64, device=dev)
@@ -144,10 +153,13 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv):
     nit = torch.zeros(B, dtype=torch.int32, device=dev)
     work = torch.empty(lib().seqm_scf_workspace(B, S, ctypes.byref(opt)), dtype=torch.uint8, device=dev)
     iters = (ctypes.c_int32 * 2)(0, 0)
+    out_ptr = ctypes.c_void_p(status.data_ptr()) if use_async else ctypes.cast(iters, ctypes.c_void_p)
     g = [_f64(x) for x in par5]
     check(lib().seqm_scf(topo.ref(), w.c, _p(_f64(M)), *[_p(x) for x in g], _p(topo.nheavy), _p(topo.nhydro),
                          _p(topo.nocc), int(topo.mmax), ctypes.byref(opt), _p(P), _p(F), _p(E), _p(nc), _p(nit),
-                         _p(pv), _p(work), iters, _stream()), 'seqm_scf')
+                         _p(pv), _p(work), out_ptr, _stream()), 'seqm_scf')
+    if use_async:
+        return P, F, E, nc.bool(), nit, None
     return P, F, E, nc.bool(), nit, (int(iters[0]), int(iters[1]))
 
 

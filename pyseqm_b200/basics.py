@@ -152,6 +152,7 @@ class Energy(torch.nn.Module):
         self.packpar = Pack_Parameters(seqm_parameters)
         self.hamiltonian = Hamiltonian(seqm_parameters)
         self.Hf_flag = seqm_parameters.get("Hf_flag", True)
+        self._defer_status = False      # Force sets this: the SCF status is then read after the backward pass
 
     def forward(self, const, coordinates, species, learned_parameters=dict(), all_terms=False, P0=None, step=0,
                 *args, **kwargs):
@@ -168,7 +169,8 @@ class Energy(torch.nn.Module):
             st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
                                self.method, run_scf=True, P0=P0, eps=H.eps_host(), sp2=H.sp2,
                                scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER,
-                               debug=_scf_loop_mod.debug, topo=prep.topo, atompar=prep.atompar, P_guess=prep.P_guess)
+                               debug=_scf_loop_mod.debug, topo=prep.topo, atompar=prep.atompar, P_guess=prep.P_guess,
+                               defer_status=self._defer_status)
         else:
             nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, atom_molid, mask, pair_molid, ni, nj, idxi, idxj, xij, rij = \
                 self.parser(const, species, coordinates, *args, **kwargs)
@@ -183,7 +185,7 @@ class Energy(torch.nn.Module):
             st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
                                self.method, run_scf=True, P0=P0, eps=H.eps_host(), sp2=H.sp2,
                                scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER,
-                               debug=_scf_loop_mod.debug)
+                               debug=_scf_loop_mod.debug, defer_status=self._defer_status)
         P, notconverged = st['P'], st['notconverged']
         Eelec, EnucAB = _ops.PairEnergy.apply(xij, rij, st)
         e = charge = None
@@ -216,13 +218,18 @@ class Force(torch.nn.Module):
 
     def forward(self, const, coordinates, species, learned_parameters=dict(), P0=None, step=0, *args, **kwargs):
         coordinates.requires_grad_(True)
-        Hf, Etot, Eelec, Enuc, Eiso, EnucAB, e, P, charge, notconverged = \
-            self.energy(const, coordinates, species, learned_parameters=learned_parameters, all_terms=True, P0=P0,
-                        step=step, *args, **kwargs)
+        self.energy._defer_status = True
+        try:
+            Hf, Etot, Eelec, Enuc, Eiso, EnucAB, e, P, charge, notconverged = \
+                self.energy(const, coordinates, species, learned_parameters=learned_parameters, all_terms=True, P0=P0,
+                            step=step, *args, **kwargs)
+        finally:
+            self.energy._defer_status = False
         L = Hf.sum()
         t0 = _engine._tic(const)
         L.backward()
         _engine._toc(const, "Force", t0)
+        _engine.resolve_status(self.energy.last_state)      # SCF status (non-convergence warning) without a mid-call sync
         force = -coordinates.grad.detach()
         coordinates.grad = torch.zeros_like(coordinates.grad)
         return force, P, Etot, Hf, Eelec, Enuc, Eiso, EnucAB, e, charge, notconverged

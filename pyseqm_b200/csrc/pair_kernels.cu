@@ -123,8 +123,11 @@ struct StoreSink {
   }
 };
 
+#ifndef SEQM_PAIRFWD_MINB
+#define SEQM_PAIRFWD_MINB 3      // resident CTAs per SM to compile for (168 registers; measured 17 % faster than 1, tools/build_variant.sh)
+#endif
 template <int CLS>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, SEQM_PAIRFWD_MINB)
 pair_fwd_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
                 const double* __restrict__ rij, int ngauss, double* __restrict__ wc, double* __restrict__ M,
                 double* __restrict__ Enuc, double* __restrict__ pairvec) {
@@ -271,8 +274,11 @@ __device__ __forceinline__ void load_diag_packed(const double* __restrict__ X, s
   for (int k = 0; k < 10; ++k) out[k] = WT(k) * base[(size_t)KN(k) * n4 + KM(k)];
 }
 
+#ifndef SEQM_PAIRGRAD_MINB
+#define SEQM_PAIRGRAD_MINB 1
+#endif
 template <int CLS>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, SEQM_PAIRGRAD_MINB)
 pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
                  const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
                  const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,

@@ -258,6 +258,11 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
                           opt->alpha, opt->eps, max_iter_s, eigh_tolerance(), P, F, Eelec, nc, niter, pairvec, wk.Pold,
                           wk.Pnew, wk.FOCK, wk.FPPF, wk.EMAT, wk.Vstore, wk.stat, wk.mol_atom0, wk.nn, st);
     if (rc) return rc;
+    if (opt->async_status) {
+      SEQM_REQUIRE(iterations_out, "seqm_scf: async_status needs the page-locked status buffer");
+      SEQM_CUDA(cudaMemcpyAsync(iterations_out, wk.stat, 16, cudaMemcpyDeviceToHost, st));
+      return SEQM_OK;
+    }
     unsigned long long hs[2] = {0, 0};
     SEQM_CUDA(cudaMemcpyAsync(hs, wk.stat, 16, cudaMemcpyDeviceToHost, st));
     SEQM_CUDA(cudaStreamSynchronize(st));
