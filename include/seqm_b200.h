@@ -172,6 +172,11 @@ typedef struct {
                          stream reaches the end of the SCF */
 } seqm_scf_options_t;
 void seqm_scf_fused(int on);
+/* warps per molecule in the one-launch form and in the m <= 32 eigensolver: 1 (default) or 2 (columns of the
+ * matrices split between the two warps of a 64-thread CTA; same arithmetic and schedule; measured slower on
+ * config 2 - 2.60 ms against 2.26 ms per step - because the CTA barrier of every Jacobi round costs more than the
+ * halved FMA work saves; kept as an experiment hook). */
+void seqm_scf_warps(int n);
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);
 int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss,
              const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,

@@ -58,6 +58,8 @@ def lib():
         L.seqm_eigh_tolerance.argtypes = [ctypes.c_double]
         L.seqm_scf_fused.argtypes = [ctypes.c_int]
         L.seqm_scf_fused.restype = None
+        L.seqm_scf_warps.argtypes = [ctypes.c_int]
+        L.seqm_scf_warps.restype = None
         L.seqm_eigh_tolerance.restype = None
         L.seqm_sp2_workspace.restype = ctypes.c_size_t
         L.seqm_sp2_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64]
@@ -81,8 +83,10 @@ def lib():
         for name in EXPORTS:
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
-                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused'):
+                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps'):
                 fn.restype = ctypes.c_int
+        if os.environ.get('SEQM_SCF_WARPS'):
+            L.seqm_scf_warps(int(os.environ['SEQM_SCF_WARPS']))
         if os.environ.get('SEQM_EIGH_TOL'):
             L.seqm_eigh_tolerance(float(os.environ['SEQM_EIGH_TOL']))
         _lib = L
@@ -91,7 +95,7 @@ def lib():
 
 EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
-           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad']
+           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad']
 
 
 def check(rc, what):

@@ -244,7 +244,9 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   const size_t smem = eigh_smem_bytes(mp, Vstore != nullptr);
   prof_mark("eigh_density", st);
   int rc;
-  if (mp <= 32 && !g_force_block_jacobi)
+  if (mp <= 32 && !g_force_block_jacobi && g_scf_warps == 2 && !e_out && !v_out)
+    rc = launch_eigh_pair(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, info, Vstore, warm, g_eigh_tol_warp, st);
+  else if (mp <= 32 && !g_force_block_jacobi)
     rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 32)
     rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
