@@ -2,7 +2,7 @@
 """Benchmark of the batched SCF hot path (BASELINE.json config 2): AM1 SCF + forces for a batch of 1024
 perturbed benzene geometries (12 atoms, 30 orbitals), eigh density path; metric = SCF molecules / second.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl|water]
 
 One step = one `Force` call (Parser + pair pass + SCF + force adjoint) over the whole batch.  `value` is
 timed with the coordinates resident in HBM; `e2e` includes, every step, the host->device copy of the
@@ -465,13 +465,145 @@ def run_c60xl(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_water(args, rank, world, local_rank):
+    """Third workload (BASELINE.json configs[4]): PM3 SCF + forces of ONE (H2O)_500 cluster (1500 atoms, 3000 packed
+    orbitals), SP2 density (eps 1e-5).  One step = one `Force` call.  N > 1: STRONG scaling - every rank holds the
+    whole system (pair pass, Fock build and gradient replicated, < 10 % of the step), the SP2 multiplications are
+    tile-sharded over the ranks with ncclAllGather (pyseqm_b200.distributed.enable_sp2_sharding)."""
+    import ctypes
+    from pyseqm_b200 import _lib, synth
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.seqm_functions.constants import Constants
+    nwater = int(os.environ.get('SEQM_BENCH_WATER', '500'))
+    dev = torch.device('cuda', local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        from pyseqm_b200.distributed import disable_sp2_sharding, enable_sp2_sharding
+        dist.init_process_group('nccl', device_id=dev)
+        enable_sp2_sharding()
+    L = _lib.lib()
+    par = dict(method='PM3', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[True, 1.0e-5], elements=[0, 1, 8], learned=[],
+               pair_outer_cutoff=1.0e10)
+    sp, xyz = synth.water_cluster(nwater, seed=0)
+    species = torch.as_tensor(sp).to(dev)
+    coords_host = torch.as_tensor(xyz).pin_memory()
+    coords = coords_host.to(dev)
+    const = Constants().to(dev)
+    fm = Force(par).to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(args.warmup):
+        out = fm(const, coords.clone(), species)
+    barrier()
+    sampler.mark_begin()
+    l0 = L.seqm_launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        out = fm(const, coords.clone(), species)
+    b.record()
+    barrier()
+    launches = int(L.seqm_launch_count() - l0)
+    total_ms = a.elapsed_time(b)
+    f_host = torch.empty(1, 3 * nwater, 3).pin_memory()
+    e_host = torch.empty(1).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o = fm(const, coords_host.to(dev, non_blocking=True), species)
+        f_host.copy_(o[0], non_blocking=True)
+        e_host.copy_(o[2].detach(), non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    sampler.mark_end()
+    if rank == 0:
+        sampler.stop()
+    t = torch.tensor([total_ms, e2e_ms], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+    # per-kernel profile of one more call: collective inside, so every rank runs it; rank 0 reports
+    L.seqm_profile_enable(1 if rank == 0 else 0)
+    fm(const, coords.clone(), species)
+    torch.cuda.synchronize()
+    st = fm.energy.last_state
+    if world > 1:
+        dist.barrier()
+        disable_sp2_sharding()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    buf = ctypes.create_string_buffer(1 << 16)
+    L.seqm_profile_report(buf, len(buf))
+    L.seqm_profile_enable(0)
+    prof = {}
+    for line in buf.value.decode().splitlines():
+        nm, ms, cnt = line.rsplit(' ', 2)
+        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
+    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
+    for v in prof.values():
+        v["share"] = v["ms"] / tot_prof
+    A_ = torch.randn(4096, 4096, device=dev)
+    B_ = torch.randn(4096, 4096, device=dev)
+    torch.matmul(A_, B_)
+    best = 1e30
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(A_, B_)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    fp64_peak = 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
+    del A_, B_
+    m = int(st['topo'].mmax)
+    spp = prof.get('sp2_step', {"ms": 0.0, "launch_groups": 1, "share": 0.0})
+    nstep = 2 * max(spp["launch_groups"], 1)                  # two purification steps per profiled group (upper bound)
+    flops = 2.0 * m ** 3                                     # SURVEY 8(d): 2 m^3 per multiplication
+    per_step = spp["ms"] / nstep
+    T_ = (m + 63) // 64
+    ach = flops / (per_step * 1e-3) / 1e12 if per_step else None
+    roof = {"bound": "tensor", "kernel": "sp2_step_kernel%s" % ("<sharded> + ncclAllGather + sp2_unpack_kernel" if world > 1 else ""),
+            "share_of_step": spp["share"], "achieved": ach, "peak": fp64_peak * world,
+            "peak_source": "cuBLAS DGEMM 4096^3 measured in this run on rank 0, times the number of GPUs",
+            "unit": "TFLOP/s", "frac": ach / (fp64_peak * world) if ach else None, "traffic": None,
+            "note": "2 m^3 flops per purification step over the time of one step (multiplication, all-gather and "
+                    "unpack) on all GPUs; %d of %d tiles executed (symmetry)" % (T_ * (T_ + 1) // 2, T_ * T_)}
+    ms_step = total_ms / args.steps
+    print(json.dumps({
+        "metric": "SCF systems/sec (one 1500-atom system, SCF + forces)", "value": 1.0 / (ms_step * 1e-3), "unit": "Force calls/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "PM3 SCF+forces, one (H2O)_%d cluster (%d atoms, %d packed orbitals), SP2 eps 1e-5, converger "
+                               "[2], scf_eps 1e-6 (BASELINE.json configs[4])" % (nwater, 3 * nwater, m),
+                   "sp2": "tile-sharded over %d GPUs, ncclAllGather" % world if world > 1 else "single GPU",
+                   "l2": "working set (X 2 x %d MB, integrals %d MB) exceeds L2" % (m * m * 8 // 10 ** 6, 900 * nwater // 500),
+                   "scf_iterations": int(st['iterations']) if st.get('iterations') is not None else None,
+                   "scf_not_converged": int(out[10].sum())},
+        "e2e": {"value": 1.0 / (e2e_ms / args.steps * 1e-3), "unit": "Force calls/s", "h2d_bytes_per_step": 3 * nwater * 24,
+                "d2h_bytes_per_step": 3 * nwater * 24 + 8},
+        "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
+        "cpu_baseline": None}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200')
-    ap.add_argument('--workload', default='benzene', choices=['benzene', 'c60xl'])
+    ap.add_argument('--workload', default='benzene', choices=['benzene', 'c60xl', 'water'])
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -480,6 +612,8 @@ def main():
         run_reference(args, rank, world)
     elif args.workload == 'c60xl':
         run_c60xl(args, rank, world, local_rank)
+    elif args.workload == 'water':
+        run_water(args, rank, world, local_rank)
     else:
         run_gpu(args, rank, world, local_rank)
 

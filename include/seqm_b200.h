@@ -149,6 +149,32 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
                      double* D, int32_t* niter, void* work, void* stream);
 
+/* Single large system (BASELINE.json configs[4]): the same purification with the 64x64 tiles of the upper block
+ * triangle of X^2 SHARDED over the GPUs of one NCCL communicator (one process per GPU).  Rank g multiplies the
+ * tiles [g*tpr, (g+1)*tpr) of the enumeration, writes each new tile and its two partial sums (diagonal, squared
+ * Frobenius norm) into a contiguous record, the records are all-gathered over NVLink (ncclAllGather, in place) and
+ * every rank unpacks all tiles and their transposes into its own copy of X; the trace rule is evaluated by every
+ * rank from the same gathered partial sums in the same order, so all ranks take identical branches and the result
+ * is bit-identical to seqm_sp2_density.  The range of a rank is cut into seqm_sp2_nccl_subchunks() pieces
+ * (default 4): the all-gather + unpack of piece k run on a side stream while piece k+1 is multiplied.
+ *   NCCL is bound at run time (dlopen of the libnccl.so.2 already in the process); the library owns the
+ *   communicator it creates:  rank 0: seqm_nccl_unique_id(id) -> broadcast the 128 bytes by any means ->
+ *   every rank: seqm_nccl_comm_create(id, rank, nranks, &comm) with its CUDA device current.
+ *   comm == NULL with emulate_ranks >= 1 runs the tile ranges of that many ranks one after the other on this GPU
+ *   through the same records and unpack kernel (test form, no NCCL).
+ *   seqm_scf_sp2_comm(comm, emulate_ranks) makes the SP2 inside seqm_scf use the sharded form (NULL, 0 restores the
+ *   single-GPU form); replaces the role of torch.matmul in reference SP2.py:47 for one large system. */
+int seqm_nccl_unique_id(void* id128);
+int seqm_nccl_comm_create(const void* id128, int rank, int nranks, void** comm_out);
+int seqm_nccl_comm_destroy(void* comm);
+void seqm_sp2_nccl_subchunks(int n);
+void seqm_sp2_shard_plan(int ntile, int nranks, int nsub, int rank, int32_t* out4); /* host only: {tiles per rank, tiles per piece, first owned tile, end} */
+size_t seqm_sp2_nccl_workspace(int64_t nmol, int64_t molsize, int nranks);
+int seqm_sp2_density_nccl(void* comm, int emulate_ranks, int64_t nmol, int64_t molsize, int mmax, const double* F,
+                          const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
+                          const uint8_t* active, double* D, int32_t* niter, void* work, void* stream);
+void seqm_scf_sp2_comm(void* comm, int emulate_ranks);
+
 /* The SCF driver: scf_forward0/1/2 (reference scf_loop.py:32-510) run device resident.
  *   converger: 0 constant mixing (alpha), 1 adaptive, 2 adaptive then Pulay
  *   P[B][n][n] in: initial guess, out: converged density; F out: fock(P) at the final density

@@ -74,6 +74,18 @@ def lib():
         L.seqm_elec_energy.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP]
         L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
         L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
+        L.seqm_nccl_unique_id.argtypes = [VP]
+        L.seqm_nccl_comm_create.argtypes = [VP, ci, ci, ctypes.POINTER(VP)]
+        L.seqm_nccl_comm_destroy.argtypes = [VP]
+        L.seqm_sp2_nccl_subchunks.argtypes = [ci]
+        L.seqm_sp2_nccl_subchunks.restype = None
+        L.seqm_sp2_shard_plan.argtypes = [ci, ci, ci, ci, c_i32p]
+        L.seqm_sp2_shard_plan.restype = None
+        L.seqm_sp2_nccl_workspace.restype = ctypes.c_size_t
+        L.seqm_sp2_nccl_workspace.argtypes = [i64, i64, ci]
+        L.seqm_sp2_density_nccl.argtypes = [VP, ci, i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
+        L.seqm_scf_sp2_comm.argtypes = [VP, ci]
+        L.seqm_scf_sp2_comm.restype = None
         L.seqm_scf.argtypes = [TP, WStore] + [VP] * 9 + [ci, ctypes.POINTER(ScfOptions)] + [VP] * 7 + \
                               [VP, VP]
         L.seqm_pair_grad.argtypes = [TP, VP, VP, VP, ci] + [VP] * 7
@@ -83,7 +95,8 @@ def lib():
         for name in EXPORTS:
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
-                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps'):
+                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps',
+                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
                 fn.restype = ctypes.c_int
         if os.environ.get('SEQM_SCF_WARPS'):
             L.seqm_scf_warps(int(os.environ['SEQM_SCF_WARPS']))
@@ -95,7 +108,9 @@ def lib():
 
 EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
-           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad']
+           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
+           'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
+           'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm']
 
 
 def check(rc, what):

@@ -112,6 +112,9 @@ def eigh_density(F, nheavy, nhydro, nocc, molsize, mmax, want_eig=False, active=
 
 
 def sp2_density(F, nheavy, nhydro, nocc, molsize, mmax, eps, active=None, want_niter=False):
+    if _sp2_shard['ranks'] >= 1 or _sp2_shard['comm'] is not None:
+        return sp2_density_sharded(F, nheavy, nhydro, nocc, molsize, mmax, eps, _sp2_shard['comm'], _sp2_shard['ranks'],
+                                   active, want_niter)
     F = _f64(F)
     B = F.shape[0]
     D = torch.zeros_like(F)
@@ -119,6 +122,49 @@ def sp2_density(F, nheavy, nhydro, nocc, molsize, mmax, eps, active=None, want_n
     nit = torch.zeros(B, dtype=torch.int32, device=F.device) if want_niter else None
     check(lib().seqm_sp2_density(B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc), float(eps),
                                  _p(active), _p(D), _p(nit), _p(work), _stream()), 'seqm_sp2_density')
+    return (D, nit) if want_niter else D
+
+
+# ---- tile-sharded SP2 (single large system over the GPUs of one box; include/seqm_b200.h, sp2_kernels.cu) ----
+_sp2_shard = {'comm': None, 'ranks': 0}      # handle of seqm_nccl_comm_create / number of (emulated) ranks
+
+
+def sp2_sharding(comm=None, ranks=0):
+    """route sp2_density() and the SP2 inside scf() through seqm_sp2_density_nccl: comm = handle from
+    nccl_comm_create(), or comm None with ranks >= 1 for the single-GPU emulation; (None, 0) switches it off"""
+    _sp2_shard['comm'], _sp2_shard['ranks'] = comm, int(ranks)
+    lib().seqm_scf_sp2_comm(comm, int(ranks))
+
+
+def nccl_unique_id():
+    buf = ctypes.create_string_buffer(128)
+    check(lib().seqm_nccl_unique_id(buf), 'seqm_nccl_unique_id')
+    return buf.raw
+
+
+def nccl_comm_create(uid, rank, nranks):
+    h = ctypes.c_void_p()
+    check(lib().seqm_nccl_comm_create(ctypes.create_string_buffer(bytes(uid), 128), int(rank), int(nranks),
+                                      ctypes.byref(h)), 'seqm_nccl_comm_create')
+    return h
+
+
+def nccl_comm_destroy(h):
+    if _sp2_shard['comm'] is h:
+        sp2_sharding(None, 0)
+    check(lib().seqm_nccl_comm_destroy(h), 'seqm_nccl_comm_destroy')
+
+
+def sp2_density_sharded(F, nheavy, nhydro, nocc, molsize, mmax, eps, comm=None, ranks=1, active=None, want_niter=False):
+    F = _f64(F)
+    B = F.shape[0]
+    D = torch.zeros_like(F)
+    nr = int(ranks) if comm is None else 64      # workspace bound; the library knows the communicator's size
+    work = torch.empty(lib().seqm_sp2_nccl_workspace(B, molsize, nr), dtype=torch.uint8, device=F.device)
+    nit = torch.zeros(B, dtype=torch.int32, device=F.device) if want_niter else None
+    check(lib().seqm_sp2_density_nccl(comm, int(ranks), B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc),
+                                      float(eps), _p(active), _p(D), _p(nit), _p(work), _stream()),
+          'seqm_sp2_density_nccl')
     return (D, nit) if want_niter else D
 
 

@@ -15,6 +15,10 @@ void set_error(const std::string& s);
 extern unsigned long long g_launches;
 void prof_mark(const char* name, cudaStream_t st);
 
+// SP2 sharding hook of the SCF driver (sp2_kernels.cu, seqm_scf_sp2_comm)
+extern void* g_scf_sp2_comm;
+extern int g_scf_sp2_nranks;
+
 inline int fail(int code, const char* what) {
   set_error(what);
   return code;

@@ -212,7 +212,9 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
     w.FPPF = (double*)take(nmol * NFOCK * nn * 8);
     w.EMAT = (double*)take(nmol * 36 * 8);
   }
-  if (opt->use_sp2) w.sp2 = take(seqm_sp2_workspace(nmol, molsize));
+  if (opt->use_sp2)
+    w.sp2 = take(g_scf_sp2_nranks >= 1 ? seqm_sp2_nccl_workspace(nmol, molsize, g_scf_sp2_nranks)
+                                       : seqm_sp2_workspace(nmol, molsize));
   else w.Vstore = (double*)take((size_t)nmol * (16 * molsize * molsize > 1024 ? 16 * molsize * molsize : 1024) * 8);
   w.total = off;
   return w;
@@ -288,6 +290,9 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
 
   int ncalls_density = 0;
   auto density = [&](double* out) -> int {
+    if (opt->use_sp2 && g_scf_sp2_nranks >= 1)      // tile-sharded over the ranks of seqm_scf_sp2_comm()
+      return seqm_sp2_density_nccl(g_scf_sp2_comm, g_scf_sp2_nranks, B, S, mmax, F, nheavy, nhydro, nocc, opt->sp2_eps,
+                                   nc, out, nullptr, wk.sp2, st);
     if (opt->use_sp2)
       return seqm_sp2_density(B, S, mmax, F, nheavy, nhydro, nocc, opt->sp2_eps, nc, out, nullptr, wk.sp2, st);
     const int warm = ncalls_density > 0 ? 1 : 0;

@@ -4,10 +4,53 @@
 // (dgemm_kernels.cu); branch choice, trace and convergence flags stay on the device, the host reads one
 // counter per iteration (the reference's `while notconverged.any()`).
 // reference: seqm/seqm_functions/SP2.py:3-72, pack.py:7-41
+#include <dlfcn.h>
+#include <cstring>
+
 #include "abi_common.cuh"
 #include "dgemm.cuh"
 
 namespace seqm {
+
+// ---- NCCL, bound at run time (the library carries no link-time dependency on it; the copy torch already
+// loaded is reused).  Only the stable entry points of nccl.h are used; the declarations below restate them.
+struct NcclUniqueId { char internal[128]; };
+typedef void* NcclComm;
+constexpr int NCCL_FLOAT64 = 8;          // ncclDataType_t::ncclFloat64
+struct NcclApi {
+  int (*GetUniqueId)(NcclUniqueId*);
+  int (*CommInitRank)(NcclComm*, int, NcclUniqueId, int);
+  int (*CommDestroy)(NcclComm);
+  int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t);
+  const char* (*GetErrorString)(int);
+  bool ok;
+};
+static NcclApi* nccl_api() {
+  static NcclApi api = [] {
+    NcclApi a{};
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return a;
+    a.GetUniqueId = (int (*)(NcclUniqueId*))dlsym(h, "ncclGetUniqueId");
+    a.CommInitRank = (int (*)(NcclComm*, int, NcclUniqueId, int))dlsym(h, "ncclCommInitRank");
+    a.CommDestroy = (int (*)(NcclComm))dlsym(h, "ncclCommDestroy");
+    a.AllGather = (int (*)(const void*, void*, size_t, int, NcclComm, cudaStream_t))dlsym(h, "ncclAllGather");
+    a.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+    a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllGather && a.GetErrorString;
+    return a;
+  }();
+  return &api;
+}
+
+// what seqm_nccl_comm_create returns: the communicator plus the side stream and events of the pipelined all-gather
+constexpr int SP2_MAXSUB = 8;
+struct SeqmComm {
+  NcclComm comm;
+  int rank, nranks;
+  cudaStream_t side;
+  cudaEvent_t computed[SP2_MAXSUB], gathered, ready;
+};
 
 struct Sp2State {      // per molecule
   double tr, e0, e1, occ;
@@ -115,23 +158,36 @@ __device__ __forceinline__ void s_dmma(double& c0, double& c1, double a, double 
                : "d"(a), "d"(b));
 }
 
+// SH = true is the tile-sharded form (single large system over several GPUs, seqm_sp2_density_nccl): this launch
+// covers the tiles [tile0, tile0 + gridDim.x) of the enumeration, the new tile and its two partial sums go into
+// a contiguous 4098-double RECORD (rec + (b * gridDim.x + blockIdx.x) * 4098) instead of X; after the all-gather
+// of the records sp2_unpack_kernel writes every tile, its transpose and the partial sums where the SH = false
+// form puts them directly.  `lead` marks the launch whose block 0 owns the per-molecule scalars.
+constexpr int SP2_REC = SBM * SBM + 2;
+
+template <bool SH>
 __global__ void __launch_bounds__(256)
 sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int32_t* __restrict__ dims,
                 const double* __restrict__ occ, double* __restrict__ Xbuf0, double* __restrict__ Xbuf1,
-                long long stride, Sp2Step* __restrict__ state, double* __restrict__ partial, int* __restrict__ nlive) {
+                long long stride, Sp2Step* __restrict__ state, double* __restrict__ partial, int* __restrict__ nlive,
+                int tile0, int lead, double* __restrict__ rec) {
   const int b = b0 + blockIdx.y;
   const Sp2Step sin = state[(size_t)(step & 1) * nmol + b];
+  const int ntile = T * (T + 1) / 2;
+  const int tileid = SH ? tile0 + (int)blockIdx.x : (int)blockIdx.x;
+  const bool leader = SH ? (lead && blockIdx.x == 0) : (blockIdx.x == 0);
+  double* myrec = SH ? rec + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC : nullptr;
   if (!sin.live) {      // keep both parities of a finished molecule identical
-    if (blockIdx.x == 0 && threadIdx.x == 0) state[(size_t)((step + 1) & 1) * nmol + b] = sin;
+    if (leader && threadIdx.x == 0) state[(size_t)((step + 1) & 1) * nmol + b] = sin;
     return;
   }
   const int nn = dims[b];
   const int TT = (nn + SBM - 1) / SBM;                      // tile rows of this molecule
   // tile id -> (ti <= tj) in the batch-wide enumeration of the upper block triangle of a T x T grid
-  int ti = 0, rem = blockIdx.x;
-  while (rem >= T - ti) { rem -= T - ti; ++ti; }
+  int ti = 0, rem = tileid;
+  if (SH && tileid >= ntile) { ti = T; rem = 0; }           // padding block of the last rank
+  while (ti < T && rem >= T - ti) { rem -= T - ti; ++ti; }
   const int tj = ti + rem;
-  const int ntile = T * (T + 1) / 2;
   const double* pin = partial + ((size_t)(step & 1) * nmol + b) * 2 * ntile;
   double* pout = partial + ((size_t)((step + 1) & 1) * nmol + b) * 2 * ntile;
   double t1 = 0.0, t2 = 0.0;
@@ -140,7 +196,7 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   const bool square = fabs(t2 - oc) < fabs(2.0 * t1 - t2 - oc);
   const double tn = square ? t2 : 2.0 * t1 - t2;
   const int tid = threadIdx.x;
-  if (blockIdx.x == 0 && tid == 0) {
+  if (leader && tid == 0) {
     Sp2Step so;
     so.e1 = sin.e0;
     so.e0 = fabs(tn - oc);
@@ -152,7 +208,10 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
     if (so.live) atomicAdd(nlive, 1);
   }
   if (ti >= TT || tj >= TT) {           // tile outside this (smaller) molecule: contributes nothing
-    if (tid == 0) { pout[2 * blockIdx.x] = 0.0; pout[2 * blockIdx.x + 1] = 0.0; }
+    if (tid == 0) {
+      if (SH) { myrec[SBM * SBM] = 0.0; myrec[SBM * SBM + 1] = 0.0; }
+      else { pout[2 * blockIdx.x] = 0.0; pout[2 * blockIdx.x + 1] = 0.0; }
+    }
     return;
   }
   const double* Xin = (sin.buf ? Xbuf1 : Xbuf0) + (size_t)b * stride;
@@ -241,6 +300,13 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   for (int idx = tid; idx < SBM * SBM; idx += 256) {
     const int rl = idx >> 6, cl = idx & 63;
     const int r = m0 + rl, c = n0 + cl;
+    if (SH) {
+      const double y = Ts[rl * SLDT + cl];          // zero outside the matrix
+      myrec[idx] = y;
+      pfr += y * y;
+      if (ti == tj && rl == cl) ptr += y;
+      continue;
+    }
     if (r < nn && c < nn) {
       const double y = Ts[rl * SLDT + cl];
       Xout[(size_t)r * ld + c] = y;
@@ -256,7 +322,48 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   __shared__ double red[8];
   ptr = blk_reduce(ptr, red, 0);
   pfr = blk_reduce(pfr, red, 0);
-  if (tid == 0) { pout[2 * blockIdx.x] = ptr; pout[2 * blockIdx.x + 1] = pfr; }
+  if (tid == 0) {
+    if (SH) { myrec[SBM * SBM] = ptr; myrec[SBM * SBM + 1] = pfr; }
+    else { pout[2 * blockIdx.x] = ptr; pout[2 * blockIdx.x + 1] = pfr; }
+  }
+}
+
+// Sharded form, after the all-gather: records of the tiles [tile0, tile0 + gridDim.x) of every molecule ->
+// X (tile and transposed tile) of the buffer this step writes, and the partial sums of the next step.
+__global__ void __launch_bounds__(256)
+sp2_unpack_kernel(int nmol, int ld, int T, int step, const int32_t* __restrict__ dims, double* __restrict__ Xbuf0,
+                  double* __restrict__ Xbuf1, long long stride, const Sp2Step* __restrict__ state,
+                  double* __restrict__ partial, int tile0, const double* __restrict__ rec) {
+  const int b = blockIdx.y;
+  const Sp2Step sin = state[(size_t)(step & 1) * nmol + b];
+  if (!sin.live) return;
+  const int ntile = T * (T + 1) / 2;
+  const int tileid = tile0 + (int)blockIdx.x;
+  if (tileid >= ntile) return;
+  const double* myrec = rec + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC;
+  double* pout = partial + ((size_t)((step + 1) & 1) * nmol + b) * 2 * ntile;
+  const int tid = threadIdx.x;
+  if (tid == 0) { pout[2 * tileid] = myrec[SBM * SBM]; pout[2 * tileid + 1] = myrec[SBM * SBM + 1]; }
+  const int nn = dims[b];
+  const int TT = (nn + SBM - 1) / SBM;
+  int ti = 0, rem = tileid;
+  while (ti < T && rem >= T - ti) { rem -= T - ti; ++ti; }
+  const int tj = ti + rem;
+  if (ti >= TT || tj >= TT) return;
+  double* Xout = (sin.buf ? Xbuf0 : Xbuf1) + (size_t)b * stride;
+  const int m0 = ti * SBM, n0 = tj * SBM;
+  __shared__ double Ts[SBM * SLDT];
+  for (int idx = tid; idx < SBM * SBM; idx += 256) Ts[(idx >> 6) * SLDT + (idx & 63)] = myrec[idx];
+  __syncthreads();
+  for (int idx = tid; idx < SBM * SBM; idx += 256) {
+    const int rl = idx >> 6, cl = idx & 63;
+    const int r = m0 + rl, c = n0 + cl;
+    if (r < nn && c < nn) Xout[(size_t)r * ld + c] = Ts[rl * SLDT + cl];
+    if (ti != tj) {
+      const int r2 = n0 + rl, c2 = m0 + cl;
+      if (r2 < nn && c2 < nn) Xout[(size_t)r2 * ld + c2] = Ts[cl * SLDT + rl];
+    }
+  }
 }
 
 // initial per-molecule scalars of the fused loop from the state sp2_init_kernel produced (X0 in buffer 0)
@@ -310,6 +417,9 @@ sp2_finish2_kernel(int S, int ld, const double* __restrict__ X0, const double* _
   }
 }
 
+void* g_scf_sp2_comm = nullptr;      // set by seqm_scf_sp2_comm(): the SCF driver's SP2 runs tile-sharded
+int g_scf_sp2_nranks = 0;
+
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static int sp2_ld(int mmax) { return (mmax + 3) & ~3; }
 static int sp2_tiles(int ld) { const int T = (ld + SBM - 1) / SBM; return T * (T + 1) / 2; }
@@ -320,19 +430,98 @@ using namespace seqm;
 
 extern "C" {
 
-size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize) {
+// tiles per rank and sub-chunk: the batch-wide enumeration [0, ntile) is cut into nranks contiguous ranges of
+// tpr = nsub * tps tiles (the last ranks may own padding tiles >= ntile)
+void seqm_sp2_shard_plan(int ntile, int nranks, int nsub, int rank, int32_t* out4) {
+  if (nranks < 1) nranks = 1;
+  if (nsub < 1) nsub = 1;
+  int tpr = (ntile + nranks - 1) / nranks;
+  const int tps = (tpr + nsub - 1) / nsub;
+  tpr = tps * nsub;
+  int lo = rank * tpr, hi = lo + tpr;
+  if (lo > ntile) lo = ntile;
+  if (hi > ntile) hi = ntile;
+  out4[0] = tpr; out4[1] = tps; out4[2] = lo; out4[3] = hi;      // owned real tiles: [lo, hi)
+}
+
+static int g_sp2_nsub = 4;
+void seqm_sp2_nccl_subchunks(int n) { g_sp2_nsub = n < 1 ? 1 : (n > SP2_MAXSUB ? SP2_MAXSUB : n); }
+
+static size_t sp2_core_bytes(int64_t nmol, int64_t molsize) {
   const size_t ld = (size_t)4 * molsize;       // upper bound of the packed size
   const size_t ntile = (size_t)sp2_tiles((int)ld);
   return 2 * al256((size_t)nmol * ld * ld * 8) + al256(nmol * sizeof(Sp2State)) + al256(nmol * 4) +
          al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + al256(nmol * 8) + 256;
 }
+static size_t sp2_record_bytes(int64_t nmol, int64_t molsize, int nranks) {
+  const size_t ntile = (size_t)sp2_tiles(4 * (int)molsize);
+  const size_t tpr_bound = (ntile + nranks - 1) / nranks + SP2_MAXSUB;      // >= tiles per rank for any sub-chunk count
+  return al256((size_t)nranks * tpr_bound * nmol * SP2_REC * 8);
+}
 
-int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
-                     const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
-                     int32_t* niter, void* work, void* stream) {
+size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize) { return sp2_core_bytes(nmol, molsize); }
+size_t seqm_sp2_nccl_workspace(int64_t nmol, int64_t molsize, int nranks) {
+  return sp2_core_bytes(nmol, molsize) + sp2_record_bytes(nmol, molsize, nranks < 1 ? 1 : nranks);
+}
+
+int seqm_nccl_unique_id(void* id128) {
+  SEQM_REQUIRE(id128, "seqm_nccl_unique_id: null pointer");
+  NcclApi* a = nccl_api();
+  if (!a->ok) return fail(SEQM_ECUDA, "seqm_nccl_unique_id: libnccl.so.2 not found");
+  NcclUniqueId id;
+  const int r = a->GetUniqueId(&id);
+  if (r) return fail(SEQM_ECUDA, a->GetErrorString(r));
+  memcpy(id128, &id, 128);
+  return SEQM_OK;
+}
+
+int seqm_nccl_comm_create(const void* id128, int rank, int nranks, void** comm_out) {
+  SEQM_REQUIRE(id128 && comm_out && nranks >= 1 && rank >= 0 && rank < nranks, "seqm_nccl_comm_create: bad argument");
+  NcclApi* a = nccl_api();
+  if (!a->ok) return fail(SEQM_ECUDA, "seqm_nccl_comm_create: libnccl.so.2 not found");
+  NcclUniqueId id;
+  memcpy(&id, id128, 128);
+  SeqmComm* c = new SeqmComm();
+  c->rank = rank; c->nranks = nranks;
+  const int r = a->CommInitRank(&c->comm, nranks, id, rank);
+  if (r) { delete c; return fail(SEQM_ECUDA, a->GetErrorString(r)); }
+  SEQM_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
+  for (int i = 0; i < SP2_MAXSUB; ++i) SEQM_CUDA(cudaEventCreateWithFlags(&c->computed[i], cudaEventDisableTiming));
+  SEQM_CUDA(cudaEventCreateWithFlags(&c->gathered, cudaEventDisableTiming));
+  SEQM_CUDA(cudaEventCreateWithFlags(&c->ready, cudaEventDisableTiming));
+  *comm_out = c;
+  return SEQM_OK;
+}
+
+int seqm_nccl_comm_destroy(void* comm) {
+  if (!comm) return SEQM_OK;
+  SeqmComm* c = (SeqmComm*)comm;
+  if (g_scf_sp2_comm == comm) { g_scf_sp2_comm = nullptr; g_scf_sp2_nranks = 0; }
+  nccl_api()->CommDestroy(c->comm);
+  cudaStreamDestroy(c->side);
+  for (int i = 0; i < SP2_MAXSUB; ++i) cudaEventDestroy(c->computed[i]);
+  cudaEventDestroy(c->gathered);
+  cudaEventDestroy(c->ready);
+  delete c;
+  return SEQM_OK;
+}
+
+// comm: handle of seqm_nccl_comm_create, or NULL with emulate_ranks >= 1: the tile ranges of `emulate_ranks`
+// ranks are computed one after the other on this GPU through the same records (test form of the sharded path)
+void seqm_scf_sp2_comm(void* comm, int emulate_ranks) {
+  g_scf_sp2_comm = comm;
+  g_scf_sp2_nranks = comm ? ((SeqmComm*)comm)->nranks : emulate_ranks;
+}
+
+// shared implementation; nranks == 0: the single-GPU form (tiles written straight into X)
+static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int mmax, const double* F,
+                   const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
+                   const uint8_t* active, double* D, int32_t* niter, void* work, void* stream) {
   SEQM_REQUIRE(F && nheavy && nhydro && nocc && D && work && nmol >= 0 && molsize > 0, "seqm_sp2_density: bad argument");
   if (nmol == 0) return SEQM_OK;
   SEQM_REQUIRE(mmax >= 1 && mmax <= 4 * molsize, "seqm_sp2_density: mmax");
+  const bool sharded = nranks >= 1;
+  SEQM_REQUIRE(!sharded || nmol <= 65535, "seqm_sp2_density_nccl: at most 65535 molecules");
   cudaStream_t st = (cudaStream_t)stream;
   if (eps < 1.0e-7) eps = 1.0e-7;      // SP2.py:21-24 (fp64 branch)
   if (eps > 1.0e-3) eps = 1.0e-3;
@@ -347,8 +536,16 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   Sp2Step* state = (Sp2Step*)base; base += al256(2 * nmol * sizeof(Sp2Step));
   double* partial = (double*)base; base += al256((size_t)2 * nmol * 2 * sp2_tiles((int)ldmax) * 8);
   double* occ = (double*)base; base += al256(nmol * 8);
-  int* nlive = (int*)base;       // [2]
+  int* nlive = (int*)base; base += 256;      // [2]
+  double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
   const long long stride = (long long)ld * ld;
+  int32_t plan[4] = {0, 0, 0, 0};
+  const int nsub = sharded ? g_sp2_nsub : 1;
+  const int myrank = cm ? cm->rank : 0;
+  if (sharded) seqm_sp2_shard_plan(ntile, nranks, nsub, myrank, plan);
+  const int tpr = plan[0], tps = plan[1];
+  const size_t seg = (size_t)B * tps * SP2_REC;      // doubles of one (sub, rank) segment
+  NcclApi* api = cm ? nccl_api() : nullptr;
   prof_mark("sp2_init", st);
   sp2_init_kernel<<<B, 256, 0, st>>>(S, ld, F, nheavy, nhydro, nocc, active, X0, init, dims);
   SEQM_CHECK_LAUNCH("sp2_init_kernel");
@@ -357,21 +554,61 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   int* hlive = nullptr;
   SEQM_CUDA(cudaMallocHost(&hlive, 2 * sizeof(int)));
   int rc = SEQM_OK;
+  auto check = [&](const char* what) {
+    cudaError_t e_ = cudaGetLastError();
+    ++g_launches;
+    if (e_ != cudaSuccess) { set_error(std::string(what) + ": " + cudaGetErrorString(e_)); rc = SEQM_ECUDA; }
+  };
+  // one purification step of the sharded form: per sub-chunk  compute (stream st) -> all-gather -> unpack
+  // (side stream), so the exchange of a sub-chunk overlaps the multiplication of the next one
+  auto sharded_step = [&](int step, int* live_counter) {
+    cudaStream_t side = cm ? cm->side : st;
+    for (int sub = 0; sub < nsub && rc == SEQM_OK; ++sub) {
+      double* subrec = records + (size_t)sub * nranks * seg;
+      const int r0 = cm ? myrank : 0, r1 = cm ? myrank + 1 : nranks;
+      for (int r = r0; r < r1 && rc == SEQM_OK; ++r) {
+        sp2_step_kernel<true><<<dim3(tps, B), 256, 0, st>>>(B, 0, ld, T, step, eps, dims, occ, X0, X1, stride, state,
+                                                          partial, live_counter, r * tpr + sub * tps,
+                                                          (sub == 0 && r == r0) ? 1 : 0, subrec + (size_t)r * seg);
+        check("sp2_step_kernel<sharded>");
+      }
+      if (rc) break;
+      if (cm) {
+        cudaEventRecord(cm->computed[sub], st);
+        cudaStreamWaitEvent(side, cm->computed[sub], 0);
+        if (nranks > 1) {
+          const int r = api->AllGather(subrec + (size_t)myrank * seg, subrec, seg, NCCL_FLOAT64, cm->comm, side);
+          if (r) { set_error(std::string("ncclAllGather: ") + api->GetErrorString(r)); rc = SEQM_ECUDA; break; }
+        }
+      }
+      for (int r = 0; r < nranks && rc == SEQM_OK; ++r) {
+        sp2_unpack_kernel<<<dim3(tps, B), 256, 0, side>>>(B, ld, T, step, dims, X0, X1, stride, state, partial,
+                                                         r * tpr + sub * tps, subrec + (size_t)r * seg);
+        check("sp2_unpack_kernel");
+      }
+    }
+    if (cm && rc == SEQM_OK) {
+      cudaEventRecord(cm->gathered, side);
+      cudaStreamWaitEvent(st, cm->gathered, 0);
+    }
+  };
+  if (cm) {      // the side stream must not run ahead of the caller's stream
+    cudaEventRecord(cm->ready, st);
+    cudaStreamWaitEvent(cm->side, cm->ready, 0);
+  }
   // two purification steps per host synchronisation: the second is a no-op (CTAs exit on the live flag) when the
   // first one finished every molecule
   for (int it = 0; it < 200 && rc == SEQM_OK; it += 2) {
     prof_mark("sp2_step", st);
     cudaMemsetAsync(nlive, 0, 2 * sizeof(int), st);
-    for (int h = 0; h < 2; ++h) {
-      for (int b0 = 0; b0 < B; b0 += 65535) {
+    for (int h = 0; h < 2 && rc == SEQM_OK; ++h) {
+      if (sharded) { sharded_step(it + h, nlive + h); continue; }
+      for (int b0 = 0; b0 < B && rc == SEQM_OK; b0 += 65535) {
         const int nb = B - b0 < 65535 ? B - b0 : 65535;
-        sp2_step_kernel<<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it + h, eps, dims, occ, X0, X1, stride, state,
-                                                        partial, nlive + h);
-        cudaError_t e_ = cudaGetLastError();
-        ++g_launches;
-        if (e_ != cudaSuccess) { set_error(std::string("sp2_step_kernel: ") + cudaGetErrorString(e_)); rc = SEQM_ECUDA; break; }
+        sp2_step_kernel<false><<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it + h, eps, dims, occ, X0, X1, stride,
+                                                               state, partial, nlive + h, 0, 1, nullptr);
+        check("sp2_step_kernel");
       }
-      if (rc) break;
     }
     if (rc) break;
     cudaMemcpyAsync(hlive, nlive, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
@@ -392,6 +629,21 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
   }
   prof_mark("end", st);
   return SEQM_OK;
+}
+
+int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                     const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
+                     int32_t* niter, void* work, void* stream) {
+  return sp2_run(nullptr, 0, nmol, molsize, mmax, F, nheavy, nhydro, nocc, eps, active, D, niter, work, stream);
+}
+
+int seqm_sp2_density_nccl(void* comm, int emulate_ranks, int64_t nmol, int64_t molsize, int mmax, const double* F,
+                          const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
+                          const uint8_t* active, double* D, int32_t* niter, void* work, void* stream) {
+  SeqmComm* cm = (SeqmComm*)comm;
+  const int nranks = cm ? cm->nranks : emulate_ranks;
+  SEQM_REQUIRE(nranks >= 1 && nranks <= 64, "seqm_sp2_density_nccl: number of ranks");
+  return sp2_run(cm, nranks, nmol, molsize, mmax, F, nheavy, nhydro, nocc, eps, active, D, niter, work, stream);
 }
 
 }  // extern "C"

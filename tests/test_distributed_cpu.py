@@ -63,3 +63,50 @@ def test_shard_and_gather_world2_gloo():
             assert p.exitcode == 0
         assert all(r[3] for r in res)
         assert res[0][1] == 0 and res[0][2] == res[1][1] and res[1][2] == nmol
+
+
+def test_sp2_tile_plan_partitions_the_upper_triangle():
+    """seqm_sp2_shard_plan (host part of the tile-sharded SP2 of config 5): contiguous ranges that cover
+    [0, ntile) exactly once, sized in whole sub-chunks"""
+    import ctypes
+    from pyseqm_b200 import _lib
+    from pyseqm_b200.distributed import sp2_tile_ranges
+    for ntile in (1, 3, 10, 1128, 4560):            # T = 1, 2, 4 (C60), 47 (config 5), 95
+        for world in (1, 2, 3, 4, 8):
+            for nsub in (1, 2, 4, 8):
+                rng = sp2_tile_ranges(ntile, world, nsub)
+                assert rng[0][0] == 0 and rng[-1][1] == ntile
+                assert all(rng[k][1] == rng[k + 1][0] for k in range(world - 1))
+                buf = (ctypes.c_int32 * 4)()
+                _lib.lib().seqm_sp2_shard_plan(ntile, world, nsub, 0, buf)
+                tpr, tps = buf[0], buf[1]
+                assert tpr == tps * nsub and tpr * world >= ntile and (tpr - nsub) * world < ntile + nsub * world
+                assert all(hi - lo <= tpr for lo, hi in rng)
+
+
+def _plan_worker(rank, world, port, ntile, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from pyseqm_b200.distributed import sp2_tile_ranges
+    lo, hi = sp2_tile_ranges(ntile, world)[rank]
+    mine = torch.zeros(ntile, dtype=torch.int64)
+    mine[lo:hi] = 1                                          # tiles this rank would multiply
+    dist.all_reduce(mine)                                    # stands for the all-gather of the tile records
+    q.put((rank, lo, hi, bool((mine == 1).all())))
+    dist.destroy_process_group()
+
+
+def test_sp2_tile_plan_world2_gloo():
+    world, ntile = 2, 1128
+    port = _free_port()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_plan_worker, args=(r, world, port, ntile, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(r[3] for r in res) and res[0][2] == res[1][1]
