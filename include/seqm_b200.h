@@ -116,16 +116,20 @@ int seqm_w_expand(const seqm_topology_t* topo, seqm_w_t w, double* w_dense, void
  *   P[B][n][n] density, M block core Hamiltonian, F[B][n][n] (out, full symmetric; must have been zero
  *   filled once by the caller: entries outside the pair pattern are never written)
  *   active[B] (may be NULL): molecules with active[b]==0 are skipped (frozen once converged)
- *   Eelec[B] (may be NULL): 0.5*sum P.(Hcore+F) for the active molecules */
+ *   Eelec[B] (may be NULL): 0.5*sum P.(Hcore+F) for the active molecules
+ *   work (may be NULL): seqm_elec_energy_workspace() bytes; with it the energy sum of a molecule is cut into
+ *   chunks of 8192 matrix elements (one CTA each, partial sums added in a fixed order) instead of one CTA per
+ *   molecule - needed when the batch is a few large molecules (config 5 is one) */
 int seqm_fock(const seqm_topology_t* topo, seqm_w_t w, const double* P, const double* M,
               const double* g_ss, const double* g_pp, const double* g_sp, const double* g_p2,
               const double* h_sp, const uint8_t* active, double* F, double* Eelec, double* pairvec,
-              void* stream);
+              void* work, void* stream);
 
 /* elec_energy() alone: E[b] = 0.5 * sum_ij P_ij (H_ij + F_ij) with H the symmetrised block matrix M.
  * xl != 0: XL-BOMD shadow energy  sum D.F - 0.5 (F-H).P  (reference XLBOMD.py:40-52), D given. */
+size_t seqm_elec_energy_workspace(int64_t nmol, int64_t molsize);
 int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
-                     const double* D, int xl, const uint8_t* active, double* E, void* stream);
+                     const double* D, int xl, const uint8_t* active, double* E, void* work, void* stream);
 
 /* sym_eig_trunc() (reference diag.py:102-172) with pack/unpack (pack.py:7-41) folded in: batched
  * symmetric eigensolver on the packed matrix (heavy atoms 4 orbitals, hydrogens 1) and

@@ -70,8 +70,10 @@ def lib():
         L.seqm_atom_pack.argtypes = [i64] + [VP] * 13 + [ci, VP, VP]
         L.seqm_hcore.argtypes = [TP, VP, VP, VP, VP, VP, ci, WStore, VP, VP, VP, VP]
         L.seqm_w_expand.argtypes = [TP, WStore, VP, VP]
-        L.seqm_fock.argtypes = [TP, WStore] + [VP] * 12
-        L.seqm_elec_energy.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP]
+        L.seqm_fock.argtypes = [TP, WStore] + [VP] * 13
+        L.seqm_elec_energy.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP, VP]
+        L.seqm_elec_energy_workspace.argtypes = [i64, i64]
+        L.seqm_elec_energy_workspace.restype = ctypes.c_size_t
         L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
         L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
         L.seqm_nccl_unique_id.argtypes = [VP]
@@ -96,7 +98,7 @@ def lib():
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
                             'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps',
-                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
+                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
                 fn.restype = ctypes.c_int
         if os.environ.get('SEQM_SCF_WARPS'):
             L.seqm_scf_warps(int(os.environ['SEQM_SCF_WARPS']))
@@ -110,7 +112,7 @@ EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
            'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
            'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
-           'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm']
+           'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace']
 
 
 def check(rc, what):

@@ -85,17 +85,26 @@ def fock(topo, w, P, M, par5, pv=None, F=None, active=None, want_energy=False):
     E = torch.zeros(topo.nmol, dtype=torch.float64, device=topo.device) if want_energy else None
     P, M = _f64(P), _f64(M)
     g = [_f64(x) for x in par5]
+    work = _energy_work(topo.nmol, topo.molsize, topo.device) if want_energy else None
     check(lib().seqm_fock(topo.ref(), w.c, _p(P), _p(M), *[_p(x) for x in g], _p(active), _p(F), _p(E), _p(pv),
-                          _stream()), 'seqm_fock')
+                          _p(work), _stream()), 'seqm_fock')
     return (F, E) if want_energy else F
+
+
+def _energy_work(nmol, molsize, device):
+    """scratch of the chunked energy sum (large molecules only; None keeps the one-CTA-per-molecule kernel)"""
+    if 4 * molsize <= 256:
+        return None
+    return torch.empty(lib().seqm_elec_energy_workspace(nmol, molsize), dtype=torch.uint8, device=device)
 
 
 def elec_energy(P, F, M, nmol, molsize, D=None):
     E = torch.zeros(nmol, dtype=torch.float64, device=P.device)
     P, F, M = _f64(P), _f64(F), _f64(M)
     Dc = _f64(D) if D is not None else None
+    work = _energy_work(nmol, molsize, P.device)
     check(lib().seqm_elec_energy(nmol, molsize, _p(P), _p(F), _p(M), _p(Dc), 1 if D is not None else 0, _p(None),
-                                 _p(E), _stream()), 'seqm_elec_energy')
+                                 _p(E), _p(work), _stream()), 'seqm_elec_energy')
     return E
 
 

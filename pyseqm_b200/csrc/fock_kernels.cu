@@ -7,6 +7,7 @@
 //   elec_energy_kernel     one CTA per molecule, 0.5 sum P.(H+F)   (or the XL-BOMD shadow energy)
 // reference: seqm/seqm_functions/fock.py:6-139, energy.py:19-36, XLBOMD.py:40-52
 #include "abi_common.cuh"
+#include "dgemm.cuh"
 
 namespace seqm {
 
@@ -191,9 +192,90 @@ elec_energy_kernel(int S, const double* __restrict__ P, const double* __restrict
   }
 }
 
+// Large molecules (one CTA per molecule would leave the GPU idle: config 5 is ONE molecule with a 6000 x 6000 padded
+// matrix): the same sum cut into chunks of RED_CHUNK elements, one CTA per (molecule, chunk), partial sums in
+// caller-provided scratch, summed in a fixed order by elec_energy_sum_kernel (deterministic, so that replicated
+// ranks of the tile-sharded SP2 take identical convergence decisions).
+__global__ void __launch_bounds__(256)
+elec_energy_part_kernel(int S, int chunks, const double* __restrict__ P, const double* __restrict__ F,
+                        const double* __restrict__ M, const double* __restrict__ D, int xl,
+                        const uint8_t* __restrict__ active, double* __restrict__ part) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  if (active && !active[mol]) return;
+  const int n4 = 4 * S;
+  const size_t nn = (size_t)n4 * n4, base = (size_t)mol * nn;
+  const size_t lo = (size_t)chunk * RED_CHUNK;
+  const size_t hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
+  double acc = 0.0;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+    const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
+    const int ai = i >> 2, mu = i & 3, aj = j >> 2, nu = j & 3;
+    double h;
+    if (ai < aj || (ai == aj && mu <= nu)) h = M[(((size_t)mol * S + ai) * S + aj) * 16 + mu * 4 + nu];
+    else h = M[(((size_t)mol * S + aj) * S + ai) * 16 + nu * 4 + mu];
+    const double f = F[base + idx], pv = P[base + idx];
+    if (xl) acc += D[base + idx] * f - 0.5 * (f - h) * pv;
+    else acc += 0.5 * pv * (h + f);
+  }
+  __shared__ double red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s_ = 0.0;
+    for (int q = 0; q < (int)(blockDim.x >> 5); ++q) s_ += red[q];
+    part[(size_t)mol * chunks + chunk] = s_;
+  }
+}
+
+// out[b * ostride] = sum of the `chunks` partial sums of item b, fixed order; one CTA per item
+__global__ void __launch_bounds__(256)
+chunk_sum_kernel(int chunks, const uint8_t* __restrict__ active, int items_per_mol, const double* __restrict__ part,
+                 double* __restrict__ out, const int32_t* __restrict__ out_index) {
+  const int b = blockIdx.x;
+  if (active && !active[b / items_per_mol]) return;
+  double acc = 0.0;
+  for (int q = threadIdx.x; q < chunks; q += blockDim.x) acc += part[(size_t)b * chunks + q];
+  __shared__ double red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s_ = 0.0;
+    for (int q = 0; q < (int)(blockDim.x >> 5); ++q) s_ += red[q];
+    out[out_index ? out_index[b] : b] = s_;
+  }
+}
+
+int red_chunks(size_t nn) { return (int)((nn + RED_CHUNK - 1) / RED_CHUNK); }
+
+int launch_chunk_sum(int items, int chunks, const uint8_t* active, int items_per_mol, const double* part, double* out,
+                     const int32_t* out_index, cudaStream_t st) {
+  chunk_sum_kernel<<<items, 256, 0, st>>>(chunks, active, items_per_mol, part, out, out_index);
+  SEQM_CHECK_LAUNCH("chunk_sum_kernel");
+  return SEQM_OK;
+}
+
+int launch_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
+                       const double* D, int xl, const uint8_t* active, double* E, double* scratch, cudaStream_t st) {
+  const size_t nn = (size_t)16 * molsize * molsize;
+  const int chunks = red_chunks(nn);
+  if (!scratch || chunks == 1) {
+    elec_energy_kernel<<<(unsigned)nmol, 256, 0, st>>>((int)molsize, P, F, M, D, xl, active, E);
+    SEQM_CHECK_LAUNCH("elec_energy_kernel");
+    return SEQM_OK;
+  }
+  SEQM_REQUIRE((long long)nmol * chunks < (1LL << 31), "elec_energy: too many chunks");
+  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, scratch);
+  SEQM_CHECK_LAUNCH("elec_energy_part_kernel");
+  return launch_chunk_sum((int)nmol, chunks, active, 1, scratch, E, nullptr, st);
+}
+
 int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const double* M, const double* g_ss,
                 const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
-                const uint8_t* active, double* F, double* Eelec, double* pairvec, cudaStream_t st) {
+                const uint8_t* active, double* F, double* Eelec, double* pairvec, double* scratch, cudaStream_t st) {
   prof_mark("fock_pair", st);
   if (t.ncls[2] > 0) {
     fock_pair_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, w.wXX, P, M, active, F, pairvec);
@@ -214,8 +296,8 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
   }
   prof_mark("elec_energy", st);
   if (Eelec && t.nmol > 0) {
-    elec_energy_kernel<<<(unsigned)t.nmol, 256, 0, st>>>((int)t.molsize, P, F, M, nullptr, 0, active, Eelec);
-    SEQM_CHECK_LAUNCH("elec_energy_kernel");
+    const int rc_ = launch_elec_energy(t.nmol, t.molsize, P, F, M, nullptr, 0, active, Eelec, scratch, st);
+    if (rc_) return rc_;
   }
   prof_mark("end", st);
   return SEQM_OK;
@@ -229,19 +311,22 @@ extern "C" {
 
 int seqm_fock(const seqm_topology_t* topo, seqm_w_t w, const double* P, const double* M, const double* g_ss,
               const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
-              const uint8_t* active, double* F, double* Eelec, double* pairvec, void* stream) {
+              const uint8_t* active, double* F, double* Eelec, double* pairvec, void* work, void* stream) {
   SEQM_REQUIRE(topo && P && M && g_ss && g_pp && g_sp && g_p2 && h_sp && F && pairvec, "seqm_fock: null pointer");
-  return launch_fock(*topo, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, active, F, Eelec, pairvec, (cudaStream_t)stream);
+  return launch_fock(*topo, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, active, F, Eelec, pairvec, (double*)work,
+                     (cudaStream_t)stream);
 }
 
 int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
-                     const double* D, int xl, const uint8_t* active, double* E, void* stream) {
+                     const double* D, int xl, const uint8_t* active, double* E, void* work, void* stream) {
   SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0, "seqm_elec_energy: bad argument");
   SEQM_REQUIRE(!xl || D, "seqm_elec_energy: xl needs D");
   if (nmol == 0) return SEQM_OK;
-  elec_energy_kernel<<<(unsigned)nmol, 256, 0, (cudaStream_t)stream>>>((int)molsize, P, F, M, D, xl, active, E);
-  SEQM_CHECK_LAUNCH("elec_energy_kernel");
-  return SEQM_OK;
+  return launch_elec_energy(nmol, molsize, P, F, M, D, xl, active, E, (double*)work, (cudaStream_t)stream);
+}
+
+size_t seqm_elec_energy_workspace(int64_t nmol, int64_t molsize) {
+  return (size_t)nmol * red_chunks((size_t)16 * molsize * molsize) * 8;
 }
 
 }  // extern "C"

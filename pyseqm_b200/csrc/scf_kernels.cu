@@ -19,38 +19,48 @@ int g_scf_fused = 1;      // 0: always the host-driven loop (test hook)
 
 enum MixMode { MIX_DIRECT = 0, MIX_CONST = 1, MIX_ADAPTIVE = 2, MIX_TAKE = 3 };
 
-// one CTA per molecule.  DIRECT: Pold = P, P = Pnew.  CONST: P = alpha P + (1-alpha) Pnew.
-// ADAPTIVE: fac from the padded diagonals, Pold = P, P = (1+fac) Pnew - fac P.  TAKE: P = Pnew.
+// DIRECT: Pold = P, P = Pnew.  CONST: P = alpha P + (1-alpha) Pnew.  ADAPTIVE: fac from the padded diagonals,
+// Pold = P, P = (1+fac) Pnew - fac P.  TAKE: P = Pnew.  All per-molecule kernels below are cut into chunks of
+// RED_CHUNK matrix elements, one CTA per (molecule, chunk): blockIdx.x = molecule * chunks + chunk.
 __global__ void __launch_bounds__(256)
-mix_kernel(int n4, int mode, double alpha, const uint8_t* __restrict__ active, const double* __restrict__ Pnew,
-           double* __restrict__ P, double* __restrict__ Pold) {
+mix_fac_kernel(int n4, const uint8_t* __restrict__ active, const double* __restrict__ Pnew,
+               const double* __restrict__ P, const double* __restrict__ Pold, double* __restrict__ fac_out) {
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const size_t base = (size_t)mol * n4 * n4;
-  const int nn = n4 * n4;
-  double fac = 0.0;
-  if (mode == MIX_ADAPTIVE) {
-    __shared__ double red[2][8];
-    double num = 0.0, den = 0.0;
-    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
-      const size_t d = base + (size_t)i * n4 + i;
-      const double dn = Pnew[d], dc = P[d], dold = Pold[d];
-      num += (dn - dc) * (dn - dc);
-      const double u = dn - dc * 2.0 + dold;
-      den += u * u;
-    }
+  __shared__ double red[2][8];
+  double num = 0.0, den = 0.0;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const size_t d = base + (size_t)i * n4 + i;
+    const double dn = Pnew[d], dc = P[d], dold = Pold[d];
+    num += (dn - dc) * (dn - dc);
+    const double u = dn - dc * 2.0 + dold;
+    den += u * u;
+  }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      num += __shfl_xor_sync(0xffffffffu, num, o);
-      den += __shfl_xor_sync(0xffffffffu, den, o);
-    }
-    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = num; red[1][threadIdx.x >> 5] = den; }
-    __syncthreads();
+  for (int o = 16; o > 0; o >>= 1) {
+    num += __shfl_xor_sync(0xffffffffu, num, o);
+    den += __shfl_xor_sync(0xffffffffu, den, o);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = num; red[1][threadIdx.x >> 5] = den; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
     num = 0.0; den = 0.0;
     for (int q = 0; q < (int)(blockDim.x >> 5); ++q) { num += red[0][q]; den += red[1][q]; }
-    fac = sqrt(num / den);
+    fac_out[mol] = sqrt(num / den);
   }
-  for (int idx = threadIdx.x; idx < nn; idx += blockDim.x) {
+}
+
+__global__ void __launch_bounds__(256)
+mix_kernel(int n4, int chunks, int mode, double alpha, const uint8_t* __restrict__ active,
+           const double* __restrict__ Pnew, double* __restrict__ P, double* __restrict__ Pold,
+           const double* __restrict__ facs) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  if (active && !active[mol]) return;
+  const size_t nn = (size_t)n4 * n4, base = (size_t)mol * nn;
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
+  const double fac = mode == MIX_ADAPTIVE ? facs[mol] : 0.0;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
     const double pn = Pnew[base + idx];
     const double pc = P[base + idx];
     if (mode == MIX_DIRECT) { Pold[base + idx] = pc; P[base + idx] = pn; }
@@ -82,31 +92,35 @@ __global__ void finish_step_kernel(int nmol, double eps, const double* __restric
 
 // Pulay store: FOCK[c] = F, FPPF[c] = triu(G - G^T) with G = F P
 __global__ void __launch_bounds__(256)
-pulay_store_kernel(int n4, int slot, const uint8_t* __restrict__ active, const double* __restrict__ F,
+pulay_store_kernel(int n4, int chunks, int slot, const uint8_t* __restrict__ active, const double* __restrict__ F,
                    const double* __restrict__ G, double* __restrict__ FOCK, double* __restrict__ FPPF) {
-  const int mol = blockIdx.x;
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
   if (active && !active[mol]) return;
   const size_t nn = (size_t)n4 * n4;
   const size_t src = (size_t)mol * nn;
   const size_t dst = ((size_t)mol * NFOCK + slot) * nn;
-  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) {
-    const int i = idx / n4, j = idx - i * n4;
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+    const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
     FOCK[dst + idx] = F[src + idx];
     FPPF[dst + idx] = (j >= i) ? G[src + idx] - G[src + (size_t)j * n4 + i] : 0.0;
   }
 }
 
-// EMAT[c][s] = <FPPF[c], FPPF[s]> for s < cF; grid (cF, nmol)
+// partial sums of EMAT[c][s] = <FPPF[c], FPPF[s]> for s < cF: blockIdx.x = (molecule * NFOCK + s) * chunks + chunk
+// (items with s >= cF are not launched: grid covers s < cF through the index arithmetic below)
 __global__ void __launch_bounds__(256)
-pulay_emat_kernel(int n4, int slot, const uint8_t* __restrict__ active, const double* __restrict__ FPPF,
-                  double* __restrict__ EMAT) {
-  const int mol = blockIdx.y, s = blockIdx.x;
+pulay_emat_part_kernel(int n4, int chunks, int cF, int slot, const uint8_t* __restrict__ active,
+                       const double* __restrict__ FPPF, double* __restrict__ part) {
+  const int item = blockIdx.x / chunks, chunk = blockIdx.x - item * chunks;
+  const int mol = item / cF, s = item - mol * cF;
   if (active && !active[mol]) return;
   const size_t nn = (size_t)n4 * n4;
   const double* a = FPPF + ((size_t)mol * NFOCK + slot) * nn;
   const double* b = FPPF + ((size_t)mol * NFOCK + s) * nn;
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   double acc = 0.0;
-  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) acc += a[idx] * b[idx];
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) acc += a[idx] * b[idx];
   __shared__ double red[8];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -115,19 +129,25 @@ pulay_emat_kernel(int n4, int slot, const uint8_t* __restrict__ active, const do
   if (threadIdx.x == 0) {
     double t = 0.0;
     for (int q = 0; q < (int)(blockDim.x >> 5); ++q) t += red[q];
-    EMAT[(size_t)mol * 36 + slot * 6 + s] = t;
+    part[(size_t)item * chunks + chunk] = t;
   }
 }
 
-// EVEC = EMAT + tril(EMAT,-1)^T; EVEC[:cF,:cF] /= EVEC[c][c]; coeff = -inverse(EVEC[:cF+1,:cF+1])[:-1,-1];
-// F = sum_s coeff_s FOCK[s]
-__global__ void __launch_bounds__(256)
-pulay_extrapolate_kernel(int n4, int slot, int cF, const uint8_t* __restrict__ active,
-                         const double* __restrict__ EMAT, const double* __restrict__ FOCK, double* __restrict__ F) {
-  const int mol = blockIdx.x;
+// where item (molecule, s) of the partial sums lands in EMAT: EMAT[mol][slot][s]
+__global__ void pulay_emat_index_kernel(int nitems, int cF, int slot, int32_t* __restrict__ index) {
+  const int item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= nitems) return;
+  const int mol = item / cF, s = item - mol * cF;
+  index[item] = mol * 36 + slot * 6 + s;
+}
+
+// EVEC = EMAT + tril(EMAT,-1)^T; EVEC[:cF,:cF] /= EVEC[c][c]; coeff = -inverse(EVEC[:cF+1,:cF+1])[:-1,-1]
+__global__ void pulay_coeff_kernel(int nmol, int slot, int cF, const uint8_t* __restrict__ active,
+                                   const double* __restrict__ EMAT, double* __restrict__ coeff) {
+  const int mol = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mol >= nmol) return;
   if (active && !active[mol]) return;
-  __shared__ double coeff[NFOCK];
-  if (threadIdx.x == 0) {
+  {
     const double* em = EMAT + (size_t)mol * 36;
     const int d = cF + 1;
     double a[6][7];
@@ -159,15 +179,28 @@ pulay_extrapolate_kernel(int n4, int slot, int cF, const uint8_t* __restrict__ a
       for (int j = r + 1; j < d; ++j) sum -= a[r][j] * x[j];
       x[r] = sum / a[r][r];
     }
-    for (int s = 0; s < cF; ++s) coeff[s] = -x[s];
+    for (int s = 0; s < cF; ++s) coeff[(size_t)mol * NFOCK + s] = -x[s];
   }
-  __syncthreads();
+}
+
+// F = sum_s coeff_s FOCK[s]
+__global__ void __launch_bounds__(256)
+pulay_extrapolate_kernel(int n4, int chunks, int cF, const uint8_t* __restrict__ active,
+                         const double* __restrict__ coeffs, const double* __restrict__ FOCK, double* __restrict__ F) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  if (active && !active[mol]) return;
+  double coeff[NFOCK];
+#pragma unroll
+  for (int s = 0; s < NFOCK; ++s) coeff[s] = s < cF ? coeffs[(size_t)mol * NFOCK + s] : 0.0;
   const size_t nn = (size_t)n4 * n4;
   const double* fo = FOCK + (size_t)mol * NFOCK * nn;
   double* out = F + (size_t)mol * nn;
-  for (int idx = threadIdx.x; idx < (int)nn; idx += blockDim.x) {
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
     double acc = 0.0;
-    for (int s = 0; s < cF; ++s) acc += fo[(size_t)s * nn + idx] * coeff[s];
+#pragma unroll
+    for (int s = 0; s < NFOCK; ++s)
+      if (s < cF) acc += fo[(size_t)s * nn + idx] * coeff[s];
     out[idx] = acc;
   }
 }
@@ -186,6 +219,8 @@ __global__ void init_flags_kernel(int nmol, uint8_t* nc, double* err, int32_t* n
 
 struct ScfWork {
   double *Pnew, *Pold, *Enew, *err, *G, *FOCK, *FPPF, *EMAT, *Vstore;
+  double *red, *fac, *coeff;      // chunked-reduction partial sums [B][NFOCK][chunks], mixing factors [B], DIIS coefficients [B][NFOCK]
+  int32_t* emat_index;
   unsigned long long* stat;
   int32_t* mol_atom0;
   char* sp2;
@@ -206,6 +241,10 @@ static ScfWork carve(char* base, int64_t nmol, int64_t molsize, const seqm_scf_o
   w.err = (double*)take(nmol * 8);
   w.stat = (unsigned long long*)take(64);
   w.mol_atom0 = (int32_t*)take(scf_small_scratch_bytes(nmol));
+  w.red = (double*)take((size_t)nmol * NFOCK * red_chunks(nn) * 8);
+  w.fac = (double*)take(nmol * 8);
+  w.coeff = (double*)take(nmol * NFOCK * 8);
+  w.emat_index = (int32_t*)take(nmol * NFOCK * 4);
   if (opt->converger == 2) {
     w.G = (double*)take(nmol * nn * 8);
     w.FOCK = (double*)take(nmol * NFOCK * nn * 8);
@@ -279,7 +318,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   init_flags_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, nc, wk.err, niter, wk.EMAT);
   SEQM_CHECK_LAUNCH("init_flags_kernel");
   // F = fock(P), Eelec
-  rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, st);
+  rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, wk.red, st);
   if (rc) return rc;
 
   unsigned long long* hstat = nullptr;
@@ -299,19 +338,29 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     ++ncalls_density;
     return launch_eigh_density(B, S, mmax, F, nheavy, nhydro, nocc, nc, out, nullptr, nullptr, nullptr, wk.Vstore, warm, st);
   };
+  const int chunks = red_chunks(nn);
+  SEQM_REQUIRE((size_t)B * NFOCK * chunks < ((size_t)1 << 31), "seqm_scf: batch too large for the chunked kernels");
+  // FOCK[slot] = F, FPPF[slot] = triu(FP - PF) (G = F P given), EMAT[slot][s] = <FPPF[slot], FPPF[s]>, s < cF
+  auto pulay_store = [&](int slot, int cF_) -> int {
+    prof_mark("pulay_store", st);
+    pulay_store_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, slot, nc, F, wk.G, wk.FOCK, wk.FPPF);
+    SEQM_CHECK_LAUNCH("pulay_store_kernel");
+    pulay_emat_part_kernel<<<(unsigned)((size_t)B * cF_ * chunks), 256, 0, st>>>(n4, chunks, cF_, slot, nc, wk.FPPF, wk.red);
+    SEQM_CHECK_LAUNCH("pulay_emat_part_kernel");
+    pulay_emat_index_kernel<<<cdiv((long long)B * cF_, 256), 256, 0, st>>>(B * cF_, cF_, slot, wk.emat_index);
+    SEQM_CHECK_LAUNCH("pulay_emat_index_kernel");
+    return launch_chunk_sum(B * cF_, chunks, nc, cF_, wk.red, wk.EMAT, wk.emat_index, st);
+  };
   auto refock_and_finish = [&](bool store, int& counter, int& cF) -> int {
-    int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, st);
+    int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, wk.red, st);
     if (r) return r;
     if (store) {
       cF = cF < NFOCK ? cF + 1 : NFOCK;
       counter = (counter + 1) % NFOCK;
       r = launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st);
       if (r) return r;
-      prof_mark("pulay_store", st);
-      pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
-      SEQM_CHECK_LAUNCH("pulay_store_kernel");
-      pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
-      SEQM_CHECK_LAUNCH("pulay_emat_kernel");
+      r = pulay_store(counter, cF);
+      if (r) return r;
     }
     prof_mark("finish+host_sync", st);
     SEQM_CUDA(cudaMemsetAsync(wk.stat, 0, 16, st));
@@ -332,7 +381,11 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   };
   auto mix = [&](int mode) -> int {
     prof_mark("mix", st);
-    mix_kernel<<<B, 256, 0, st>>>(n4, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold);
+    if (mode == MIX_ADAPTIVE) {
+      mix_fac_kernel<<<B, 256, 0, st>>>(n4, nc, wk.Pnew, P, wk.Pold, wk.fac);
+      SEQM_CHECK_LAUNCH("mix_fac_kernel");
+    }
+    mix_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold, wk.fac);
     SEQM_CHECK_LAUNCH("mix_kernel");
     return SEQM_OK;
   };
@@ -372,16 +425,15 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
         cF = cF < NFOCK ? cF + 1 : NFOCK;
         counter = (counter + 1) % NFOCK;
         SEQM_TRY(launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st));
-        prof_mark("pulay_store", st);
-        pulay_store_kernel<<<B, 256, 0, st>>>(n4, counter, nc, F, wk.G, wk.FOCK, wk.FPPF);
-        pulay_emat_kernel<<<dim3(cF, B), 256, 0, st>>>(n4, counter, nc, wk.FPPF, wk.EMAT);
-        { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay store: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
+        SEQM_TRY(pulay_store(counter, cF));
         SEQM_TRY(density(P));
         SEQM_TRY(refock_and_finish(false, counter, cF));
       }
       while (left > 0) {
         prof_mark("pulay_extrapolate", st);
-        pulay_extrapolate_kernel<<<B, 256, 0, st>>>(n4, counter, cF, nc, wk.EMAT, wk.FOCK, F);
+        pulay_coeff_kernel<<<cdiv(B, 128), 128, 0, st>>>(B, counter, cF, nc, wk.EMAT, wk.coeff);
+        pulay_extrapolate_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, cF, nc, wk.coeff, wk.FOCK, F);
+        g_launches += 2;
         { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
         SEQM_TRY(density(P));
         SEQM_TRY(refock_and_finish(true, counter, cF));

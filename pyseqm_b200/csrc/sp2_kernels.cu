@@ -73,59 +73,92 @@ __device__ __forceinline__ double blk_reduce(double v, double* red, int op) {   
   return s;
 }
 
-// one CTA per molecule: Gershgorin bounds of the packed matrix, X0, trace
+// Initialisation, cut so that ONE large molecule still fills the GPU (config 5 is a single 3000 x 3000 matrix):
+//   sp2_bounds_kernel  warp per packed row (8 rows per CTA): Gershgorin interval of the row -> per-CTA min / max
+//   sp2_x0_kernel      CTA per chunk of RED_CHUNK elements of X: h1, hN from the per-CTA bounds (every CTA reduces
+//                      the same numbers in the same order), X0 = (hN I - F)/(hN - h1), partial trace and |X0|_F^2
+//   sp2_step_init_kernel  CTA per molecule: sums the partials in a fixed order, initial state of the fused loop
+constexpr int SP2_ROWS = 8;
+
 __global__ void __launch_bounds__(256)
-sp2_init_kernel(int S, int ld, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
-                const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
-                const uint8_t* __restrict__ active, double* __restrict__ X, Sp2State* __restrict__ st,
-                int32_t* __restrict__ dims) {
-  const int mol = blockIdx.x;
+sp2_bounds_kernel(int S, int rchunks, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
+                  const int32_t* __restrict__ nhydro, const uint8_t* __restrict__ active, double* __restrict__ bounds,
+                  int32_t* __restrict__ dims) {
+  const int mol = blockIdx.x / rchunks, chunk = blockIdx.x - mol * rchunks;
   const int nh4 = 4 * nheavy[mol];
   const int m = nh4 + nhydro[mol];
-  if (threadIdx.x == 0) dims[mol] = m;
-  const bool on = (!active || active[mol]) && m > 0;
-  if (!on) {
-    if (threadIdx.x == 0) { st[mol].live = 0; st[mol].niter = 0; }
-    return;
-  }
-  __shared__ double red[8];
+  if (chunk == 0 && threadIdx.x == 0) dims[mol] = m;
+  if ((active && !active[mol]) || m <= 0) return;
   const int n4 = 4 * S;
   const double* Fm = F + (size_t)mol * n4 * n4;
-  double* Xm = X + (size_t)mol * ld * ld;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int i = chunk * SP2_ROWS + warp;
   double lo = 1.0e300, hi = -1.0e300;
-  for (int i = threadIdx.x; i < m; i += blockDim.x) {
-    const int pi = pk2pad(i, nh4);
+  if (i < m) {
+    const size_t row = (size_t)pk2pad(i, nh4) * n4;
     double rad = 0.0, aii = 0.0;
-    for (int j = 0; j < m; ++j) {
-      const double a = Fm[(size_t)pi * n4 + pk2pad(j, nh4)];
+    for (int j = lane; j < m; j += 32) {
+      const double a = Fm[row + pk2pad(j, nh4)];
       if (j == i) aii = a; else rad += fabs(a);
     }
-    lo = fmin(lo, aii - rad);
-    hi = fmax(hi, aii + rad);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      rad += __shfl_xor_sync(0xffffffffu, rad, o);
+      aii += __shfl_xor_sync(0xffffffffu, aii, o);
+    }
+    lo = aii - rad;
+    hi = aii + rad;
+  }
+  __shared__ double slo[SP2_ROWS], shi[SP2_ROWS];
+  if (lane == 0) { slo[warp] = lo; shi[warp] = hi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int q = 1; q < SP2_ROWS; ++q) { lo = fmin(lo, slo[q]); hi = fmax(hi, shi[q]); }
+    bounds[((size_t)mol * rchunks + chunk) * 2] = lo;
+    bounds[((size_t)mol * rchunks + chunk) * 2 + 1] = hi;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sp2_x0_kernel(int S, int ld, int rchunks, int chunks, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
+              const int32_t* __restrict__ nhydro, const uint8_t* __restrict__ active, const double* __restrict__ bounds,
+              double* __restrict__ X, double* __restrict__ part) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  const int nh4 = 4 * nheavy[mol];
+  const int m = nh4 + nhydro[mol];
+  if ((active && !active[mol]) || m <= 0) return;
+  __shared__ double red[8];
+  const int mr = (m + SP2_ROWS - 1) / SP2_ROWS;       // row chunks that hold rows of this molecule
+  double lo = 1.0e300, hi = -1.0e300;
+  for (int q = threadIdx.x; q < mr; q += blockDim.x) {
+    lo = fmin(lo, bounds[((size_t)mol * rchunks + q) * 2]);
+    hi = fmax(hi, bounds[((size_t)mol * rchunks + q) * 2 + 1]);
   }
   const double h1 = blk_reduce(lo, red, 1);
   const double hN = blk_reduce(hi, red, 2);
   const double sc = hN - h1;
-  double tr = 0.0;
-  for (int idx = threadIdx.x; idx < ld * ld; idx += blockDim.x) {
-    const int i = idx / ld, j = idx - i * ld;
+  const int n4 = 4 * S;
+  const double* Fm = F + (size_t)mol * n4 * n4;
+  double* Xm = X + (size_t)mol * ld * ld;
+  const size_t tot = (size_t)ld * ld;
+  const size_t e0 = (size_t)chunk * RED_CHUNK, e1 = e0 + RED_CHUNK < tot ? e0 + RED_CHUNK : tot;
+  double tr = 0.0, fr = 0.0;
+  for (size_t idx = e0 + threadIdx.x; idx < e1; idx += blockDim.x) {
+    const int i = (int)(idx / ld), j = (int)(idx - (size_t)i * ld);
     double x = 0.0;
     if (i < m && j < m) {
       const double a = Fm[(size_t)pk2pad(i, nh4) * n4 + pk2pad(j, nh4)];
       x = ((i == j ? hN : 0.0) - a) / sc;
       if (i == j) tr += x;
+      fr += x * x;
     }
     Xm[idx] = x;
   }
   tr = blk_reduce(tr, red, 0);
+  fr = blk_reduce(fr, red, 0);
   if (threadIdx.x == 0) {
-    Sp2State s;
-    s.occ = (double)nocc[mol];
-    s.tr = tr;
-    s.e0 = fabs(tr - s.occ);
-    s.e1 = s.e0;
-    s.live = 1; s.niter = 0; s.square = 0; s.pad = 0;
-    st[mol] = s;
+    part[((size_t)mol * chunks + chunk) * 2] = tr;
+    part[((size_t)mol * chunks + chunk) * 2 + 1] = fr;
   }
 }
 
@@ -366,33 +399,35 @@ sp2_unpack_kernel(int nmol, int ld, int T, int step, const int32_t* __restrict__
   }
 }
 
-// initial per-molecule scalars of the fused loop from the state sp2_init_kernel produced (X0 in buffer 0)
-__global__ void sp2_step_init_kernel(int nmol, int ntile, int ld, const int32_t* __restrict__ dims,
-                                     const Sp2State* __restrict__ st, const double* __restrict__ X, long long stride,
-                                     Sp2Step* __restrict__ state, double* __restrict__ partial, double* __restrict__ occ) {
+// initial per-molecule scalars of the fused loop from the partial sums sp2_x0_kernel left (X0 in buffer 0)
+__global__ void __launch_bounds__(256)
+sp2_step_init_kernel(int nmol, int ntile, int chunks, const int32_t* __restrict__ dims,
+                     const int32_t* __restrict__ nocc, const uint8_t* __restrict__ active,
+                     const double* __restrict__ part, Sp2Step* __restrict__ state, double* __restrict__ partial,
+                     double* __restrict__ occ) {
   const int b = blockIdx.x;
   __shared__ double red[8];
-  const int m = dims[b];
-  const bool live = st[b].live != 0;
-  double fr = 0.0;
+  const bool live = (!active || active[b]) && dims[b] > 0;
+  double tr = 0.0, fr = 0.0;
   if (live) {
-    const double* Xm = X + (size_t)b * stride;
-    for (int idx = threadIdx.x; idx < m * m; idx += blockDim.x) {
-      const int i = idx / m, j = idx - i * m;
-      const double x = Xm[(size_t)i * ld + j];
-      fr += x * x;
+    for (int q = threadIdx.x; q < chunks; q += blockDim.x) {
+      tr += part[((size_t)b * chunks + q) * 2];
+      fr += part[((size_t)b * chunks + q) * 2 + 1];
     }
   }
+  tr = blk_reduce(tr, red, 0);
   fr = blk_reduce(fr, red, 0);
+  for (int q = threadIdx.x; q < 2 * ntile; q += blockDim.x) partial[(size_t)b * 2 * ntile + q] = 0.0;
+  __syncthreads();
   if (threadIdx.x == 0) {
+    const double oc = (double)nocc[b];
     Sp2Step s;
-    s.e0 = st[b].e0; s.e1 = st[b].e1; s.live = live ? 1 : 0; s.niter = 0; s.buf = 0; s.pad = 0;
+    s.e0 = fabs(tr - oc); s.e1 = s.e0; s.live = live ? 1 : 0; s.niter = 0; s.buf = 0; s.pad = 0;
     state[b] = s;
     s.live = 0;
     state[(size_t)nmol + b] = s;
-    occ[b] = st[b].occ;
-    for (int q = 0; q < 2 * ntile; ++q) partial[(size_t)b * 2 * ntile + q] = 0.0;
-    partial[(size_t)b * 2 * ntile] = st[b].tr;
+    occ[b] = oc;
+    partial[(size_t)b * 2 * ntile] = tr;
     partial[(size_t)b * 2 * ntile + 1] = fr;
   }
 }
@@ -422,6 +457,7 @@ int g_scf_sp2_nranks = 0;
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static int sp2_ld(int mmax) { return (mmax + 3) & ~3; }
+static int sp2_rchunks(int ld) { return (ld + SP2_ROWS - 1) / SP2_ROWS; }
 static int sp2_tiles(int ld) { const int T = (ld + SBM - 1) / SBM; return T * (T + 1) / 2; }
 
 }  // namespace seqm
@@ -450,8 +486,9 @@ void seqm_sp2_nccl_subchunks(int n) { g_sp2_nsub = n < 1 ? 1 : (n > SP2_MAXSUB ?
 static size_t sp2_core_bytes(int64_t nmol, int64_t molsize) {
   const size_t ld = (size_t)4 * molsize;       // upper bound of the packed size
   const size_t ntile = (size_t)sp2_tiles((int)ld);
-  return 2 * al256((size_t)nmol * ld * ld * 8) + al256(nmol * sizeof(Sp2State)) + al256(nmol * 4) +
-         al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + al256(nmol * 8) + 256;
+  return 2 * al256((size_t)nmol * ld * ld * 8) + al256((size_t)nmol * sp2_rchunks((int)ld) * 16) + al256(nmol * 4) +
+         al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + al256(nmol * 8) + 256 +
+         al256((size_t)nmol * red_chunks(ld * ld) * 16);
 }
 static size_t sp2_record_bytes(int64_t nmol, int64_t molsize, int nranks) {
   const size_t ntile = (size_t)sp2_tiles(4 * (int)molsize);
@@ -531,12 +568,13 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   char* base = (char*)work;
   double* X0 = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
   double* X1 = (double*)base; base += al256((size_t)nmol * ldmax * ldmax * 8);
-  Sp2State* init = (Sp2State*)base; base += al256(nmol * sizeof(Sp2State));
+  double* bounds = (double*)base; base += al256((size_t)nmol * sp2_rchunks((int)ldmax) * 16);
   int32_t* dims = (int32_t*)base; base += al256(nmol * 4);
   Sp2Step* state = (Sp2Step*)base; base += al256(2 * nmol * sizeof(Sp2Step));
   double* partial = (double*)base; base += al256((size_t)2 * nmol * 2 * sp2_tiles((int)ldmax) * 8);
   double* occ = (double*)base; base += al256(nmol * 8);
   int* nlive = (int*)base; base += 256;      // [2]
+  double* part0 = (double*)base; base += al256((size_t)nmol * red_chunks(ldmax * ldmax) * 16);
   double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
   const long long stride = (long long)ld * ld;
   int32_t plan[4] = {0, 0, 0, 0};
@@ -547,9 +585,13 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   const size_t seg = (size_t)B * tps * SP2_REC;      // doubles of one (sub, rank) segment
   NcclApi* api = cm ? nccl_api() : nullptr;
   prof_mark("sp2_init", st);
-  sp2_init_kernel<<<B, 256, 0, st>>>(S, ld, F, nheavy, nhydro, nocc, active, X0, init, dims);
-  SEQM_CHECK_LAUNCH("sp2_init_kernel");
-  sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, ld, dims, init, X0, stride, state, partial, occ);
+  const int rchunks = sp2_rchunks(ld), xchunks = red_chunks((size_t)ld * ld);
+  SEQM_REQUIRE((long long)B * rchunks < (1LL << 31) && (long long)B * xchunks < (1LL << 31), "seqm_sp2_density: batch too large");
+  sp2_bounds_kernel<<<(unsigned)((size_t)B * rchunks), 256, 0, st>>>(S, rchunks, F, nheavy, nhydro, active, bounds, dims);
+  SEQM_CHECK_LAUNCH("sp2_bounds_kernel");
+  sp2_x0_kernel<<<(unsigned)((size_t)B * xchunks), 256, 0, st>>>(S, ld, rchunks, xchunks, F, nheavy, nhydro, active, bounds, X0, part0);
+  SEQM_CHECK_LAUNCH("sp2_x0_kernel");
+  sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, xchunks, dims, nocc, active, part0, state, partial, occ);
   SEQM_CHECK_LAUNCH("sp2_step_init_kernel");
   int* hlive = nullptr;
   SEQM_CUDA(cudaMallocHost(&hlive, 2 * sizeof(int)));
