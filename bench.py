@@ -483,6 +483,8 @@ def run_water(args, rank, world, local_rank):
         dist.init_process_group('nccl', device_id=dev)
         enable_sp2_sharding()
     L = _lib.lib()
+    if os.environ.get('SEQM_SP2_NSUB'):
+        L.seqm_sp2_nccl_subchunks(int(os.environ['SEQM_SP2_NSUB']))
     par = dict(method='PM3', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[True, 1.0e-5], elements=[0, 1, 8], learned=[],
                pair_outer_cutoff=1.0e10)
     sp, xyz = synth.water_cluster(nwater, seed=0)

@@ -159,8 +159,9 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
  * Frobenius norm) into a contiguous record, the records are all-gathered over NVLink (ncclAllGather, in place) and
  * every rank unpacks all tiles and their transposes into its own copy of X; the trace rule is evaluated by every
  * rank from the same gathered partial sums in the same order, so all ranks take identical branches and the result
- * is bit-identical to seqm_sp2_density.  The range of a rank is cut into seqm_sp2_nccl_subchunks() pieces
- * (default 4): the all-gather + unpack of piece k run on a side stream while piece k+1 is multiplied.
+ * is bit-identical to seqm_sp2_density.  The range of a rank is cut into pieces (seqm_sp2_nccl_subchunks(n), n = 0:
+ * automatic - as many, up to 4, as still leave 148 x 4 tiles per launch): the all-gather + unpack of piece k run on a
+ * side stream while piece k+1 is multiplied.
  *   NCCL is bound at run time (dlopen of the libnccl.so.2 already in the process); the library owns the
  *   communicator it creates:  rank 0: seqm_nccl_unique_id(id) -> broadcast the 128 bytes by any means ->
  *   every rank: seqm_nccl_comm_create(id, rank, nranks, &comm) with its CUDA device current.

@@ -480,8 +480,15 @@ void seqm_sp2_shard_plan(int ntile, int nranks, int nsub, int rank, int32_t* out
   out4[0] = tpr; out4[1] = tps; out4[2] = lo; out4[3] = hi;      // owned real tiles: [lo, hi)
 }
 
-static int g_sp2_nsub = 4;
-void seqm_sp2_nccl_subchunks(int n) { g_sp2_nsub = n < 1 ? 1 : (n > SP2_MAXSUB ? SP2_MAXSUB : n); }
+static int g_sp2_nsub = 0;      // 0: automatic
+void seqm_sp2_nccl_subchunks(int n) { g_sp2_nsub = n < 0 ? 0 : (n > SP2_MAXSUB ? SP2_MAXSUB : n); }
+// automatic choice: a piece must still fill the GPU (148 SMs x 4 resident CTAs of sp2_step_kernel), otherwise
+// the multiplication loses more to idle SMs than the overlap of the exchange wins
+static int sp2_auto_nsub(int ntile, int nranks, int nmol) {
+  const long long per_rank = ((long long)(ntile + nranks - 1) / nranks) * nmol;
+  long long n = per_rank / (148 * 4);
+  return n < 1 ? 1 : (n > 4 ? 4 : (int)n);
+}
 
 static size_t sp2_core_bytes(int64_t nmol, int64_t molsize) {
   const size_t ld = (size_t)4 * molsize;       // upper bound of the packed size
@@ -578,7 +585,7 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
   const long long stride = (long long)ld * ld;
   int32_t plan[4] = {0, 0, 0, 0};
-  const int nsub = sharded ? g_sp2_nsub : 1;
+  const int nsub = !sharded ? 1 : (g_sp2_nsub > 0 ? g_sp2_nsub : sp2_auto_nsub(ntile, nranks, B));
   const int myrank = cm ? cm->rank : 0;
   if (sharded) seqm_sp2_shard_plan(ntile, nranks, nsub, myrank, plan);
   const int tpr = plan[0], tps = plan[1];
