@@ -483,6 +483,8 @@ def run_water(args, rank, world, local_rank):
         dist.init_process_group('nccl', device_id=dev)
         enable_sp2_sharding()
     L = _lib.lib()
+    if os.environ.get('SEQM_SP2_P2P'):
+        L.seqm_sp2_nccl_p2p(int(os.environ['SEQM_SP2_P2P']))
     if os.environ.get('SEQM_SP2_NSUB'):
         L.seqm_sp2_nccl_subchunks(int(os.environ['SEQM_SP2_NSUB']))
     par = dict(method='PM3', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[True, 1.0e-5], elements=[0, 1, 8], learned=[],
@@ -587,7 +589,7 @@ def run_water(args, rank, world, local_rank):
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "PM3 SCF+forces, one (H2O)_%d cluster (%d atoms, %d packed orbitals), SP2 eps 1e-5, converger "
                                "[2], scf_eps 1e-6 (BASELINE.json configs[4])" % (nwater, 3 * nwater, m),
-                   "sp2": "tile-sharded over %d GPUs, ncclAllGather" % world if world > 1 else "single GPU",
+                   "sp2": ("tile-sharded over %d GPUs, %s" % (world, "ncclAllGather of the tile records" if os.environ.get('SEQM_SP2_P2P') == '0' else "records stored peer to peer over NVLink by the multiplication kernel")) if world > 1 else "single GPU",
                    "l2": "working set (X 2 x %d MB, integrals %d MB) exceeds L2" % (m * m * 8 // 10 ** 6, 900 * nwater // 500),
                    "scf_iterations": int(st['iterations']) if st.get('iterations') is not None else None,
                    "scf_not_converged": int(out[10].sum())},

@@ -168,7 +168,14 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
  *   comm == NULL with emulate_ranks >= 1 runs the tile ranges of that many ranks one after the other on this GPU
  *   through the same records and unpack kernel (test form, no NCCL).
  *   seqm_scf_sp2_comm(comm, emulate_ranks) makes the SP2 inside seqm_scf use the sharded form (NULL, 0 restores the
- *   single-GPU form); replaces the role of torch.matmul in reference SP2.py:47 for one large system. */
+ *   single-GPU form); replaces the role of torch.matmul in reference SP2.py:47 for one large system.
+ *   Default with a communicator of <= 16 ranks: the PEER-TO-PEER form - the library allocates the record buffers
+ *   itself, maps every rank's buffer into every process (CUDA IPC handles exchanged through the communicator) and
+ *   the multiplication kernel stores each finished record directly into all ranks' buffers over NVLink, so the
+ *   exchange overlaps the multiplication tile by tile inside ONE launch; an 8-byte all-gather serves as the barrier
+ *   before the unpack.  seqm_sp2_nccl_p2p(0), more than 16 ranks or a failed IPC mapping select the ncclAllGather
+ *   form described above. */
+void seqm_sp2_nccl_p2p(int on);
 int seqm_nccl_unique_id(void* id128);
 int seqm_nccl_comm_create(const void* id128, int rank, int nranks, void** comm_out);
 int seqm_nccl_comm_destroy(void* comm);

@@ -50,6 +50,12 @@ struct SeqmComm {
   int rank, nranks;
   cudaStream_t side;
   cudaEvent_t computed[SP2_MAXSUB], gathered, ready;
+  // peer-to-peer form: record buffers owned by the library (two step parities), mapped into every rank with CUDA IPC
+  bool p2p_tried, p2p;
+  size_t rec_cap;                  // doubles per parity
+  double* rec_own;                 // cudaMalloc: 2 * rec_cap doubles
+  double* rec_peer[16];            // rank q's rec_own as seen from this process (own rank: rec_own)
+  double* bar;                     // [2 * nranks] doubles: barrier payload
 };
 
 struct Sp2State {      // per molecule
@@ -197,19 +203,22 @@ __device__ __forceinline__ void s_dmma(double& c0, double& c1, double a, double 
 // of the records sp2_unpack_kernel writes every tile, its transpose and the partial sums where the SH = false
 // form puts them directly.  `lead` marks the launch whose block 0 owns the per-molecule scalars.
 constexpr int SP2_REC = SBM * SBM + 2;
+constexpr int SP2_MAXPEER = 16;
+struct Sp2Peers { double* p[SP2_MAXPEER]; int n; };
 
 template <bool SH>
 __global__ void __launch_bounds__(256)
 sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int32_t* __restrict__ dims,
                 const double* __restrict__ occ, double* __restrict__ Xbuf0, double* __restrict__ Xbuf1,
                 long long stride, Sp2Step* __restrict__ state, double* __restrict__ partial, int* __restrict__ nlive,
-                int tile0, int lead, double* __restrict__ rec) {
+                int tile0, int lead, Sp2Peers peers, size_t recoff) {
   const int b = b0 + blockIdx.y;
   const Sp2Step sin = state[(size_t)(step & 1) * nmol + b];
   const int ntile = T * (T + 1) / 2;
   const int tileid = SH ? tile0 + (int)blockIdx.x : (int)blockIdx.x;
   const bool leader = SH ? (lead && blockIdx.x == 0) : (blockIdx.x == 0);
-  double* myrec = SH ? rec + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC : nullptr;
+  // the record of this tile inside every destination buffer (own GPU and, in the peer-to-peer form, every peer)
+  const size_t myoff = SH ? recoff + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC : 0;
   if (!sin.live) {      // keep both parities of a finished molecule identical
     if (leader && threadIdx.x == 0) state[(size_t)((step + 1) & 1) * nmol + b] = sin;
     return;
@@ -242,7 +251,9 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   }
   if (ti >= TT || tj >= TT) {           // tile outside this (smaller) molecule: contributes nothing
     if (tid == 0) {
-      if (SH) { myrec[SBM * SBM] = 0.0; myrec[SBM * SBM + 1] = 0.0; }
+      if (SH) {
+        for (int q = 0; q < peers.n; ++q) { peers.p[q][myoff + SBM * SBM] = 0.0; peers.p[q][myoff + SBM * SBM + 1] = 0.0; }
+      }
       else { pout[2 * blockIdx.x] = 0.0; pout[2 * blockIdx.x + 1] = 0.0; }
     }
     return;
@@ -335,7 +346,7 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
     const int r = m0 + rl, c = n0 + cl;
     if (SH) {
       const double y = Ts[rl * SLDT + cl];          // zero outside the matrix
-      myrec[idx] = y;
+      for (int q = 0; q < peers.n; ++q) peers.p[q][myoff + idx] = y;      // NVLink stores for q != own rank
       pfr += y * y;
       if (ti == tj && rl == cl) ptr += y;
       continue;
@@ -356,7 +367,9 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   ptr = blk_reduce(ptr, red, 0);
   pfr = blk_reduce(pfr, red, 0);
   if (tid == 0) {
-    if (SH) { myrec[SBM * SBM] = ptr; myrec[SBM * SBM + 1] = pfr; }
+    if (SH) {
+      for (int q = 0; q < peers.n; ++q) { peers.p[q][myoff + SBM * SBM] = ptr; peers.p[q][myoff + SBM * SBM + 1] = pfr; }
+    }
     else { pout[2 * blockIdx.x] = ptr; pout[2 * blockIdx.x + 1] = pfr; }
   }
 }
@@ -527,6 +540,8 @@ int seqm_nccl_comm_create(const void* id128, int rank, int nranks, void** comm_o
   memcpy(&id, id128, 128);
   SeqmComm* c = new SeqmComm();
   c->rank = rank; c->nranks = nranks;
+  c->p2p_tried = c->p2p = false; c->rec_cap = 0; c->rec_own = nullptr; c->bar = nullptr;
+  for (int i = 0; i < 16; ++i) c->rec_peer[i] = nullptr;
   const int r = a->CommInitRank(&c->comm, nranks, id, rank);
   if (r) { delete c; return fail(SEQM_ECUDA, a->GetErrorString(r)); }
   SEQM_CUDA(cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking));
@@ -541,6 +556,13 @@ int seqm_nccl_comm_destroy(void* comm) {
   if (!comm) return SEQM_OK;
   SeqmComm* c = (SeqmComm*)comm;
   if (g_scf_sp2_comm == comm) { g_scf_sp2_comm = nullptr; g_scf_sp2_nranks = 0; }
+  cudaDeviceSynchronize();
+  if (c->rec_own) {
+    for (int q = 0; q < c->nranks && q < 16; ++q)
+      if (q != c->rank && c->rec_peer[q]) cudaIpcCloseMemHandle(c->rec_peer[q]);
+    cudaFree(c->rec_own);
+  }
+  if (c->bar) cudaFree(c->bar);
   nccl_api()->CommDestroy(c->comm);
   cudaStreamDestroy(c->side);
   for (int i = 0; i < SP2_MAXSUB; ++i) cudaEventDestroy(c->computed[i]);
@@ -555,6 +577,69 @@ int seqm_nccl_comm_destroy(void* comm) {
 void seqm_scf_sp2_comm(void* comm, int emulate_ranks) {
   g_scf_sp2_comm = comm;
   g_scf_sp2_nranks = comm ? ((SeqmComm*)comm)->nranks : emulate_ranks;
+}
+
+static int g_sp2_p2p = 1;
+void seqm_sp2_nccl_p2p(int on) { g_sp2_p2p = on; }
+static size_t seg_full(int B, int tpr) { return (size_t)B * tpr * SP2_REC; }
+
+// Record buffers of the peer-to-peer form: allocated by the library (cudaMalloc, two step parities), their CUDA IPC
+// handles all-gathered through NCCL and opened by every rank.  Collective: every rank calls it with the same size.
+// Returns false (and the caller uses ncclAllGather on the torch-owned records) if any rank could not map a peer.
+static bool sp2_p2p_ready(SeqmComm* cm, size_t doubles) {
+  if (!g_sp2_p2p || cm->nranks > SP2_MAXPEER) return false;
+  if (cm->p2p_tried && (!cm->p2p || cm->rec_cap >= doubles)) return cm->p2p;
+  NcclApi* api = nccl_api();
+  const int n = cm->nranks;
+  if (cm->rec_own) {      // grow: unmap, free, start again (all ranks take this branch together)
+    cudaDeviceSynchronize();
+    for (int q = 0; q < n; ++q)
+      if (q != cm->rank && cm->rec_peer[q]) cudaIpcCloseMemHandle(cm->rec_peer[q]);
+    cudaFree(cm->rec_own);
+    cm->rec_own = nullptr;
+  }
+  cm->p2p_tried = true;
+  cm->p2p = false;
+  cm->rec_cap = (doubles + 511) & ~(size_t)511;
+  bool ok = cudaMalloc(&cm->rec_own, 2 * cm->rec_cap * 8) == cudaSuccess;
+  if (!cm->bar) ok = ok && cudaMalloc(&cm->bar, (size_t)(2 * n + 16 * n + 2 * n) * 8) == cudaSuccess;
+  // exchange {ok flag, 64-byte IPC handle} = 9 doubles per rank, staged through cm->bar + 2n
+  double* xbuf = cm->bar ? cm->bar + 2 * n : nullptr;
+  double hostx[SP2_MAXPEER * 9];
+  memset(hostx, 0, sizeof(hostx));
+  cudaIpcMemHandle_t h;
+  memset(&h, 0, sizeof(h));
+  if (ok) ok = cudaIpcGetMemHandle(&h, cm->rec_own) == cudaSuccess;
+  double mine[9];
+  mine[0] = ok ? 1.0 : 0.0;
+  memcpy(mine + 1, &h, 64);
+  if (!xbuf) { cudaGetLastError(); return false; }
+  cudaMemcpy(xbuf + 9 * cm->rank, mine, 72, cudaMemcpyHostToDevice);
+  if (api->AllGather(xbuf + 9 * cm->rank, xbuf, 9, NCCL_FLOAT64, cm->comm, cm->side)) { cudaGetLastError(); return false; }
+  cudaStreamSynchronize(cm->side);
+  cudaMemcpy(hostx, xbuf, (size_t)n * 72, cudaMemcpyDeviceToHost);
+  bool all = true;
+  for (int q = 0; q < n; ++q) all = all && hostx[9 * q] == 1.0;
+  double opened = 1.0;
+  for (int q = 0; q < n && all; ++q) {
+    if (q == cm->rank) { cm->rec_peer[q] = cm->rec_own; continue; }
+    cudaIpcMemHandle_t hq;
+    memcpy(&hq, hostx + 9 * q + 1, 64);
+    void* ptr = nullptr;
+    if (cudaIpcOpenMemHandle(&ptr, hq, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { opened = 0.0; cm->rec_peer[q] = nullptr; }
+    else cm->rec_peer[q] = (double*)ptr;
+  }
+  // second round: did every rank map every peer?
+  double* flags = xbuf + 9 * n;
+  cudaMemcpy(flags + cm->rank, &opened, 8, cudaMemcpyHostToDevice);
+  if (api->AllGather(flags + cm->rank, flags, 1, NCCL_FLOAT64, cm->comm, cm->side)) { cudaGetLastError(); return false; }
+  cudaStreamSynchronize(cm->side);
+  double hf[SP2_MAXPEER];
+  cudaMemcpy(hf, flags, (size_t)n * 8, cudaMemcpyDeviceToHost);
+  for (int q = 0; q < n; ++q) all = all && hf[q] == 1.0;
+  cudaGetLastError();      // a failed IPC call must not poison later launch checks
+  cm->p2p = all;
+  return all;
 }
 
 // shared implementation; nranks == 0: the single-GPU form (tiles written straight into X)
@@ -585,7 +670,8 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
   const long long stride = (long long)ld * ld;
   int32_t plan[4] = {0, 0, 0, 0};
-  const int nsub = !sharded ? 1 : (g_sp2_nsub > 0 ? g_sp2_nsub : sp2_auto_nsub(ntile, nranks, B));
+  const bool want_p2p = cm && nranks > 1 && nranks <= SP2_MAXPEER && g_sp2_p2p;
+  const int nsub = (!sharded || want_p2p) ? 1 : (g_sp2_nsub > 0 ? g_sp2_nsub : sp2_auto_nsub(ntile, nranks, B));
   const int myrank = cm ? cm->rank : 0;
   if (sharded) seqm_sp2_shard_plan(ntile, nranks, nsub, myrank, plan);
   const int tpr = plan[0], tps = plan[1];
@@ -616,9 +702,12 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
       double* subrec = records + (size_t)sub * nranks * seg;
       const int r0 = cm ? myrank : 0, r1 = cm ? myrank + 1 : nranks;
       for (int r = r0; r < r1 && rc == SEQM_OK; ++r) {
+        Sp2Peers one{};
+        one.n = 1;
+        one.p[0] = subrec + (size_t)r * seg;
         sp2_step_kernel<true><<<dim3(tps, B), 256, 0, st>>>(B, 0, ld, T, step, eps, dims, occ, X0, X1, stride, state,
                                                           partial, live_counter, r * tpr + sub * tps,
-                                                          (sub == 0 && r == r0) ? 1 : 0, subrec + (size_t)r * seg);
+                                                          (sub == 0 && r == r0) ? 1 : 0, one, 0);
         check("sp2_step_kernel<sharded>");
       }
       if (rc) break;
@@ -641,6 +730,29 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
       cudaStreamWaitEvent(st, cm->gathered, 0);
     }
   };
+  // peer-to-peer form (default with a communicator): ONE launch multiplies all tiles of this rank and stores every
+  // new record straight into the record buffer of every rank over NVLink (the exchange overlaps the multiplication
+  // tile by tile, no collective moves data); an 8-byte all-gather is the barrier, then every rank unpacks
+  const bool p2p = want_p2p && sp2_p2p_ready(cm, (size_t)nranks * seg_full(B, tpr));
+  auto p2p_step = [&](int step, int* live_counter) {
+    const size_t segf = seg_full(B, tpr);
+    Sp2Peers peers{};
+    peers.n = nranks;
+    for (int q = 0; q < nranks; ++q) peers.p[q] = cm->rec_peer[q] + (size_t)(step & 1) * cm->rec_cap;
+    sp2_step_kernel<true><<<dim3(tpr, B), 256, 0, st>>>(B, 0, ld, T, step, eps, dims, occ, X0, X1, stride, state, partial,
+                                                      live_counter, myrank * tpr, 1, peers, (size_t)myrank * segf);
+    check("sp2_step_kernel<p2p>");
+    if (rc) return;
+    double* bar = cm->bar + (size_t)(step & 1) * nranks;
+    const int r = api->AllGather(bar + myrank, bar, 1, NCCL_FLOAT64, cm->comm, st);
+    if (r) { set_error(std::string("ncclAllGather (barrier): ") + api->GetErrorString(r)); rc = SEQM_ECUDA; return; }
+    const double* mine = cm->rec_own + (size_t)(step & 1) * cm->rec_cap;
+    for (int q = 0; q < nranks && rc == SEQM_OK; ++q) {
+      sp2_unpack_kernel<<<dim3(tpr, B), 256, 0, st>>>(B, ld, T, step, dims, X0, X1, stride, state, partial, q * tpr,
+                                                     mine + (size_t)q * segf);
+      check("sp2_unpack_kernel");
+    }
+  };
   if (cm) {      // the side stream must not run ahead of the caller's stream
     cudaEventRecord(cm->ready, st);
     cudaStreamWaitEvent(cm->side, cm->ready, 0);
@@ -651,11 +763,12 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
     prof_mark("sp2_step", st);
     cudaMemsetAsync(nlive, 0, 2 * sizeof(int), st);
     for (int h = 0; h < 2 && rc == SEQM_OK; ++h) {
+      if (p2p) { p2p_step(it + h, nlive + h); continue; }
       if (sharded) { sharded_step(it + h, nlive + h); continue; }
       for (int b0 = 0; b0 < B && rc == SEQM_OK; b0 += 65535) {
         const int nb = B - b0 < 65535 ? B - b0 : 65535;
         sp2_step_kernel<false><<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it + h, eps, dims, occ, X0, X1, stride,
-                                                               state, partial, nlive + h, 0, 1, nullptr);
+                                                               state, partial, nlive + h, 0, 1, Sp2Peers{}, 0);
         check("sp2_step_kernel");
       }
     }
