@@ -379,14 +379,17 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
 __global__ void __launch_bounds__(256)
 sp2_unpack_kernel(int nmol, int ld, int T, int step, const int32_t* __restrict__ dims, double* __restrict__ Xbuf0,
                   double* __restrict__ Xbuf1, long long stride, const Sp2Step* __restrict__ state,
-                  double* __restrict__ partial, int tile0, const double* __restrict__ rec) {
+                  double* __restrict__ partial, int tile0, const double* __restrict__ rec, int tpr) {
+  // tpr > 0: one launch over the segments of ALL ranks, layout [rank][molecule][tpr] (peer-to-peer form)
   const int b = blockIdx.y;
   const Sp2Step sin = state[(size_t)(step & 1) * nmol + b];
   if (!sin.live) return;
   const int ntile = T * (T + 1) / 2;
   const int tileid = tile0 + (int)blockIdx.x;
   if (tileid >= ntile) return;
-  const double* myrec = rec + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC;
+  const double* myrec = tpr > 0
+      ? rec + (((size_t)(blockIdx.x / tpr) * gridDim.y + b) * tpr + (blockIdx.x % tpr)) * SP2_REC
+      : rec + ((size_t)b * gridDim.x + blockIdx.x) * SP2_REC;
   double* pout = partial + ((size_t)((step + 1) & 1) * nmol + b) * 2 * ntile;
   const int tid = threadIdx.x;
   if (tid == 0) { pout[2 * tileid] = myrec[SBM * SBM]; pout[2 * tileid + 1] = myrec[SBM * SBM + 1]; }
@@ -721,7 +724,7 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
       }
       for (int r = 0; r < nranks && rc == SEQM_OK; ++r) {
         sp2_unpack_kernel<<<dim3(tps, B), 256, 0, side>>>(B, ld, T, step, dims, X0, X1, stride, state, partial,
-                                                         r * tpr + sub * tps, subrec + (size_t)r * seg);
+                                                         r * tpr + sub * tps, subrec + (size_t)r * seg, 0);
         check("sp2_unpack_kernel");
       }
     }
@@ -747,11 +750,8 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
     const int r = api->AllGather(bar + myrank, bar, 1, NCCL_FLOAT64, cm->comm, st);
     if (r) { set_error(std::string("ncclAllGather (barrier): ") + api->GetErrorString(r)); rc = SEQM_ECUDA; return; }
     const double* mine = cm->rec_own + (size_t)(step & 1) * cm->rec_cap;
-    for (int q = 0; q < nranks && rc == SEQM_OK; ++q) {
-      sp2_unpack_kernel<<<dim3(tpr, B), 256, 0, st>>>(B, ld, T, step, dims, X0, X1, stride, state, partial, q * tpr,
-                                                     mine + (size_t)q * segf);
-      check("sp2_unpack_kernel");
-    }
+    sp2_unpack_kernel<<<dim3(nranks * tpr, B), 256, 0, st>>>(B, ld, T, step, dims, X0, X1, stride, state, partial, 0, mine, tpr);
+    check("sp2_unpack_kernel");
   };
   if (cm) {      // the side stream must not run ahead of the caller's stream
     cudaEventRecord(cm->ready, st);
