@@ -283,6 +283,19 @@ def run_gpu(args, rank, world, local_rank):
     top = max(share, key=share.get)
     roof = {"bound": "hbm", "kernel": top, "share_of_step": share[top], "achieved": kernels[top]["achieved_gbs"],
             "peak": hbm, "peak_source": peak_src, "unit": "GB/s", "frac": kernels[top]["frac_of_hbm"], "traffic": None}
+    if top == 'scf_small':
+        # ncu --set full of this kernel on this workload (profiles/r01p_scf_small_ncu.txt): DRAM bytes per launch and
+        # what actually bounds it - neither roofline: 6.9 warps per SM, FP64 pipe 19 % busy, issue slots 26 % busy
+        m_, B_ = int(topo.mmax), int(topo.nmol)
+        iters = int(st['iterations']) + 1
+        flops = B_ * iters * (9.0 * m_ ** 3 + 2.0 * m_ * m_ * int(topo.nocc.max()))      # 9 m^3 + 2 m^2 nocc per eigensolve
+        roof.update({"traffic": 198338048 + 125199872,
+                     "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch (cold-cache replay), "
+                                       "profiles/r01p_scf_small_ncu.txt",
+                     "limiter": "latency of one warp per molecule (ncu: sm__pipe_fp64_cycles_active 19.5 %, "
+                                "smsp__issue_active 26.0 %, stalls short_scoreboard / wait / long_scoreboard)",
+                     "algorithmic_tflops": flops / (kernels[top]["ms_per_launch"] * 1e-3) / 1e12,
+                     "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
     # ---- CPU baseline: the oracle port on a bounded sample, all host cores ----
     sys.path.insert(0, os.path.join(ROOT, 'oracle'))
     import seqm_oracle as orc
@@ -431,7 +444,9 @@ def run_c60xl(args, rank, world, local_rank):
             "achieved": flops / (per_launch * 1e-3) / 1e12 if per_launch else None, "peak": fp64_peak,
             "peak_source": "cuBLAS DGEMM 4096^3 measured in this run (MEASURED_PEAKS.json holds no FP64 number)",
             "unit": "TFLOP/s", "frac": flops / (per_launch * 1e-3) / 1e12 / fp64_peak if per_launch else None,
-            "traffic": None,
+            "traffic": (118043904 + 79299328) if nmol == 256 else None,
+            "traffic_source": "ncu dram bytes of one sp2_step_kernel launch, profiles/r01p_c60_ncu.txt (top stall: "
+                              "math_pipe_throttle, tensor pipe = DMMA)",
             "note": "algorithmic flops 2 m^3 per product; the kernel executes %d of %d tiles (symmetry), i.e. %.3f of "
                     "them; the last launch of the loop may be a no-op" % (T_ * (T_ + 1) // 2, T_ * T_,
                                                                         (T_ + 1) / (2.0 * T_))}
@@ -579,7 +594,10 @@ def run_water(args, rank, world, local_rank):
     roof = {"bound": "tensor", "kernel": "sp2_step_kernel%s" % ("<sharded> + ncclAllGather + sp2_unpack_kernel" if world > 1 else ""),
             "share_of_step": spp["share"], "achieved": ach, "peak": fp64_peak * world,
             "peak_source": "cuBLAS DGEMM 4096^3 measured in this run on rank 0, times the number of GPUs",
-            "unit": "TFLOP/s", "frac": ach / (fp64_peak * world) if ach else None, "traffic": None,
+            "unit": "TFLOP/s", "frac": ach / (fp64_peak * world) if ach else None,
+            "traffic": (181162752 + 51730432) if (world == 1 and nwater == 500) else None,
+            "traffic_source": "ncu dram bytes of one single-GPU sp2_step_kernel launch, profiles/r01p_sp2_step_water_ncu.txt "
+                              "(sm__pipe_tensor_cycles_active 61 %, top stall math_pipe_throttle)",
             "note": "2 m^3 flops per purification step over the time of one step (multiplication, all-gather and "
                     "unpack) on all GPUs; %d of %d tiles executed (symmetry)" % (T_ * (T_ + 1) // 2, T_ * T_)}
     ms_step = total_ms / args.steps
