@@ -2,7 +2,7 @@
 """Benchmark of the batched SCF hot path (BASELINE.json config 2): AM1 SCF + forces for a batch of 1024
 perturbed benzene geometries (12 atoms, 30 orbitals), eigh density path; metric = SCF molecules / second.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl|water]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl|water|organics]
 
 One step = one `Force` call (Parser + pair pass + SCF + force adjoint) over the whole batch.  `value` is
 timed with the coordinates resident in HBM; `e2e` includes, every step, the host->device copy of the
@@ -619,13 +619,151 @@ def run_water(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_organics(args, rank, world, local_rank):
+    """Fourth workload (BASELINE.json configs[3]): MNDO SCF + forces over 65,536 mixed organics of 5-30 atoms (library of
+    2048 grown molecules x 32 perturbed copies), eigh density.  STRONG scaling: the batch is cut into contiguous molecule
+    ranges, one per rank (pyseqm_b200.distributed.shard_batch); every rank runs its shard as a size-bucketed sweep
+    (pyseqm_b200.batching.BucketedBatch); one all_gather of the energies ends the step.  One step = the whole sweep."""
+    import ctypes
+    from pyseqm_b200 import _lib, synth
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.batching import BucketedBatch
+    from pyseqm_b200.distributed import gather_molecules, shard_bounds
+    from pyseqm_b200.seqm_functions.constants import Constants
+    ntotal = int(os.environ.get('SEQM_BENCH_ORGANICS', '65536'))
+    dev = torch.device('cuda', local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
+    L = _lib.lib()
+    par = dict(method='MNDO', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6, 7, 8], learned=[],
+               pair_outer_cutoff=1.0e10)
+    sp, xyz = synth.mixed_organics_sweep(ntotal, seed=0)
+    lo, hi = shard_bounds(ntotal, world)[rank]
+    species = torch.as_tensor(sp[lo:hi]).to(dev)
+    coords_host = torch.as_tensor(xyz[lo:hi]).pin_memory()
+    coords = coords_host.to(dev)
+    nloc = hi - lo
+    const = Constants().to(dev)
+    fm = Force(par).to(dev)
+    bb = BucketedBatch(species)
+
+    def step(x):
+        f, Etot, Hf, nc = bb.run(fm, const, x)
+        if world > 1:
+            gather_molecules(Etot, ntotal, world)
+        return f, Etot, nc
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(args.warmup):
+        f, Etot, nc = step(coords)
+    nfail = int(nc.sum())
+    barrier()
+    sampler.mark_begin()
+    l0 = L.seqm_launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        step(coords)
+    b.record()
+    barrier()
+    launches = int(L.seqm_launch_count() - l0)
+    total_ms = a.elapsed_time(b)
+    f_host = torch.empty(nloc, 30, 3).pin_memory()
+    e_host = torch.empty(nloc).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        f, Etot, nc = step(coords_host.to(dev, non_blocking=True))
+        f_host.copy_(f, non_blocking=True)
+        e_host.copy_(Etot, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    sampler.mark_end()
+    if rank == 0:
+        sampler.stop()
+    t = torch.tensor([total_ms, e2e_ms, float(nfail)], device=dev)
+    if world > 1:
+        dist.all_reduce(t[:2], op=dist.ReduceOp.MAX)
+        nf = t[2:].clone()
+        dist.all_reduce(nf)
+        t[2] = nf[0]
+    total_ms, e2e_ms, nfail = float(t[0]), float(t[1]), int(t[2])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    L.seqm_profile_enable(1)
+    bb.run(fm, const, coords)
+    torch.cuda.synchronize()
+    buf = ctypes.create_string_buffer(1 << 16)
+    L.seqm_profile_report(buf, len(buf))
+    L.seqm_profile_enable(0)
+    prof = {}
+    for line in buf.value.decode().splitlines():
+        nm, ms, cnt = line.rsplit(' ', 2)
+        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
+    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
+    for v in prof.values():
+        v["share"] = v["ms"] / tot_prof
+    top = max(prof, key=lambda k: prof[k]["ms"])
+    hbm, peak_src = peaks()
+    # integrals + matrices each SCF kernel must move at least once (DESIGN.md section 4), summed over the buckets
+    alg = 0
+    for idx, bsp in bb.buckets:
+        nx, nh = (bsp > 1).sum(1), (bsp == 1).sum(1)
+        m = 4 * nx + nh
+        alg += int((nx * (nx - 1) // 2 * 800 + nx * nh * 80 + nh * (nh - 1) // 2 * 8 + 4 * m * m * 8 + (nx + nh) * 40).sum())
+    small_ms = prof.get('scf_small', {"ms": 0.0})["ms"]
+    roof = {"bound": "hbm", "kernel": top, "share_of_step": prof[top]["share"],
+            "achieved": alg / (tot_prof * 1e-3) / 1e9, "peak": hbm, "peak_source": peak_src, "unit": "GB/s",
+            "frac": alg / (tot_prof * 1e-3) / 1e9 / hbm, "traffic": None,
+            "note": "algorithmic bytes of the whole sweep (integrals once + 4 packed matrices per molecule) over the sum of "
+                    "the profiled kernel times of one sweep; the SCF kernels are latency / FP64-issue bound (DESIGN.md), "
+                    "one-launch warp SCF %.1f ms of %.1f ms" % (small_ms, tot_prof)}
+    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+    import seqm_oracle as orc
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ns = 512
+    t0 = time.time()
+    orc.run(torch.as_tensor(sp[:ns]), torch.as_tensor(xyz[:ns]), method='MNDO', scf_eps=1e-6, converger=(2, 0.0))
+    cpu_s = time.time() - t0
+    ms_step = total_ms / args.steps
+    print(json.dumps({
+        "metric": "SCF molecules/sec", "value": ntotal / (ms_step * 1e-3), "unit": "molecules/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "MNDO SCF+forces sweep, %d mixed organics of 5-30 atoms (2048 grown molecules x perturbed "
+                               "copies), eigh, converger [2], scf_eps 1e-6, sharded by molecule over %d GPU(s) "
+                               "(BASELINE.json configs[3])" % (ntotal, world),
+                   "molecules_per_gpu": nloc, "buckets_rank0": bb.summary(),
+                   "l2": "working set of a sweep (integrals + matrices of %d molecules) exceeds L2" % nloc,
+                   "scf_not_converged": nfail},
+        "e2e": {"value": ntotal / (e2e_ms / args.steps * 1e-3), "unit": "molecules/s",
+                "h2d_bytes_per_step": nloc * 30 * 3 * 8, "d2h_bytes_per_step": nloc * 30 * 3 * 8 + nloc * 8},
+        "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
+        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": "port",
+                         "sample": "the first %d molecules of the sweep, one Force-equivalent call of the oracle" % ns}}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200')
-    ap.add_argument('--workload', default='benzene', choices=['benzene', 'c60xl', 'water'])
+    ap.add_argument('--workload', default='benzene', choices=['benzene', 'c60xl', 'water', 'organics'])
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -636,6 +774,8 @@ def main():
         run_c60xl(args, rank, world, local_rank)
     elif args.workload == 'water':
         run_water(args, rank, world, local_rank)
+    elif args.workload == 'organics':
+        run_organics(args, rank, world, local_rank)
     else:
         run_gpu(args, rank, world, local_rank)
 

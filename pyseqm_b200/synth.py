@@ -180,6 +180,19 @@ def mixed_organics(nmol, seed=0, min_atoms=5, max_atoms=30):
     return _finish(species, coords)
 
 
+def mixed_organics_sweep(nmol, seed=0, base=2048, sigma=0.02, max_atoms=30):
+    """BASELINE.json configs[3] at full size without growing 65,536 molecules one by one: a library of `base`
+    grown molecules (mixed_organics), each used nmol / base times with independent N(0, sigma) displacements of
+    every real atom.  Molecule k is library entry k % base, so any contiguous shard holds the whole size mix."""
+    sp0, xyz0 = mixed_organics(min(base, nmol), seed=seed, max_atoms=max_atoms)
+    reps = (nmol + sp0.shape[0] - 1) // sp0.shape[0]
+    species = np.tile(sp0, (reps, 1))[:nmol]
+    coords = np.tile(xyz0, (reps, 1, 1))[:nmol].copy()
+    rng = np.random.RandomState(seed + 1)
+    coords += rng.normal(0.0, sigma, size=coords.shape) * (species > 0)[:, :, None]
+    return species, coords
+
+
 def formaldehyde_pair():
     """The reference's tests/test1.py molecules 0 and 2: H2CO [8,6,1,1] and the padded [8,8,6,0]."""
     species = np.array([[8, 6, 1, 1], [8, 8, 6, 0]])

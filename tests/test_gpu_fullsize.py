@@ -183,3 +183,34 @@ def test_config5_slice_water_cluster_sp2():
     Pk = _pack_density(P, species)[0]
     assert float((Pk @ Pk - 2.0 * Pk).abs().max()) < 1e-3
     _check_invariants(force, coords, species, 1e-3)
+
+
+def test_config4_bucketed_sweep_matches_plain_batch():
+    """BucketedBatch (size buckets, trimmed padding, per-bucket SCF form) gives the plain padded batch's results in the
+    caller's order; spot check against the oracle"""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'oracle'))
+    import seqm_oracle as orc
+    from pyseqm_b200 import synth
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.batching import BucketedBatch
+    from pyseqm_b200.seqm_functions.constants import Constants
+    dev = _dev()
+    par = dict(method='MNDO', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6, 7, 8], learned=[],
+               pair_outer_cutoff=1.0e10)
+    sp, xyz = synth.mixed_organics(96, seed=11)
+    species, coords = torch.as_tensor(sp).to(dev), torch.as_tensor(xyz).to(dev)
+    const = Constants().to(dev)
+    fm = Force(par).to(dev)
+    plain = fm(const, coords.clone(), species)
+    bb = BucketedBatch(species, max_chunk=16)
+    assert sum(n for n, _, _ in bb.summary()) == 96 and len(bb.buckets) >= 6
+    f, Etot, Hf, nc = bb.run(fm, const, coords)
+    assert not bool(nc.any()) and not bool(plain[10].any())
+    assert float((Etot - plain[2].detach()).abs().max()) < 2e-6
+    assert float((Hf - plain[3].detach()).abs().max()) < 2e-6
+    assert float((f - plain[0]).abs().max()) < 2e-5
+    sel = torch.tensor([0, 17, 40, 95])
+    ref = orc.run(torch.as_tensor(sp)[sel], torch.as_tensor(xyz)[sel], method='MNDO', scf_eps=1e-6, converger=(2, 0.0))
+    assert float((Etot[sel.to(dev)].cpu() - ref['Etot']).abs().max()) < 1e-5
+    assert float((f[sel.to(dev)].cpu() - ref['force']).abs().max()) < 1e-4

@@ -69,3 +69,27 @@ def test_no_cpu_fallback():
                pair_outer_cutoff=1e10)
     with pytest.raises(RuntimeError):
         Energy(par)(Constants(), torch.as_tensor(xyz), torch.as_tensor(sp_))
+
+
+def test_bucketed_batch_plan_covers_every_molecule_once():
+    """host logic of pyseqm_b200.batching (config 4 sweeps): buckets partition the batch, keep every real atom, respect
+    the size edges and the chunk cap"""
+    import numpy as np
+    import torch
+    from pyseqm_b200 import synth
+    from pyseqm_b200.batching import DEFAULT_EDGES, BucketedBatch, packed_sizes
+    sp, _ = synth.mixed_organics(200, seed=3)
+    species = torch.as_tensor(sp)
+    bb = BucketedBatch(species, max_chunk=32)
+    seen = torch.cat([idx for idx, _ in bb.buckets])
+    assert sorted(seen.tolist()) == list(range(200))
+    edges = [0] + list(DEFAULT_EDGES) + [1 << 30]
+    for idx, bsp in bb.buckets:
+        assert 0 < idx.numel() <= 32
+        assert torch.equal((bsp > 0).sum(1), (species[idx] > 0).sum(1))          # no real atom trimmed
+        assert int((bsp > 0).sum(1).max()) == bsp.shape[1]                        # padding trimmed to the bucket
+        m = packed_sizes(bsp)
+        k = int(np.searchsorted(edges, int(m.max()), side='left'))
+        assert int(m.min()) > edges[k - 1] and int(m.max()) <= edges[k]
+    sp2, xyz2 = synth.mixed_organics_sweep(100, seed=0, base=40)
+    assert sp2.shape == (100, 30) and (sp2[40:80] == sp2[:40]).all() and not np.allclose(xyz2[40:80], xyz2[:40])
