@@ -140,6 +140,7 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
 void seqm_eigh_force_block(int on); /* test hook: shared-memory (CTA) Jacobi also for m <= 32 */
+void seqm_eigh_block_config(int bits); /* shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64 */
 void seqm_eigh_tolerance(double tol); /* Jacobi stopping rule: one final sweep once off^2 <= tol * total^2 (defaults: 1e-24 CTA kernel, 1e-18 warp kernel; tol <= 0 restores them) */
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,

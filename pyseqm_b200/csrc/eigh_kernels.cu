@@ -31,7 +31,7 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return s;
 }
 
-template <int NT, int MINB>
+template <int NT, int MINB, bool FAST_T>
 __global__ void __launch_bounds__(NT, MINB)
 eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                     const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
@@ -119,8 +119,26 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
         if (apq != 0.0) {
           // t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)), theta = (aqq - app) / (2 apq), without forming theta
           const double d = A[q * ld + q] - A[p * ld + p], b = 2.0 * apq;
-          const double tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) / (fabs(d) + sqrt(d * d + b * b));
-          c = rsqrt(tt * tt + 1.0);
+          double tt;
+          if (FAST_T) {
+            // tangent in FP32 (its 1e-7 relative error only leaves a residual 1e-7 |apq| behind the rotation, which the
+            // next sweep removes); c = 1/sqrt(1 + t^2) in FP64 from that same t, so the rotation stays orthogonal to
+            // rounding (same scheme as the warp kernel, eigh_warp.cuh)
+            const float df = (float)d, bf = (float)b;
+            const float h2 = fmaxf(fmaf(df, df, bf * bf), 1.0e-37f);
+            const float den = fmaxf(fmaf(h2, __frsqrt_rn(h2), fabsf(df)), 1.0e-37f);
+            float tf = __fdividef(df >= 0.0f ? bf : -bf, den);
+            tf = fminf(fmaxf(tf, -1.0f), 1.0f);
+            tt = (double)tf;
+            const double q1 = fma(tt, tt, 1.0);
+            double y;
+            asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(q1));
+            const double e = fma(-q1 * y, y, 1.0);
+            c = fma(y * e, fma(0.375, e, 0.5), y);
+          } else {
+            tt = ((d >= 0.0) == (b >= 0.0) ? fabs(b) : -fabs(b)) / (fabs(d) + sqrt(d * d + b * b));
+            c = rsqrt(tt * tt + 1.0);
+          }
           s = tt * c;
         }
         cs[2 * tid] = c; cs[2 * tid + 1] = s;
@@ -205,6 +223,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
 double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel)
 double g_eigh_tol_warp = 1.0e-18; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
 double eigh_tolerance() { return g_eigh_tol_warp; }
+int g_eigh_cfg = 0;      // experiment hook (seqm_eigh_block_config): bit 0: 256-thread CTAs + FP32 tangent for 32 < m <= 48, bit 1: FP32 tangent for m <= 64
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {
@@ -216,16 +235,16 @@ size_t eigh_vstore_doubles(int64_t nmol, int mmax) {
   return mmax <= EIGH_WARM_MAX_M ? (size_t)nmol * mp * mp : 0;
 }
 
-template <int NT, int MINB>
+template <int NT, int MINB, bool FAST_T>
 static int launch_cfg(int64_t nmol, size_t smem, cudaStream_t st, int S, int mp, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
                       double* v_out, int32_t* info, double* Vstore, int warm, double tol) {
   static thread_local size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB, FAST_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  eigh_density_kernel<NT, MINB><<<(unsigned)nmol, NT, smem, st>>>(S, mp, F, nheavy, nhydro, nocc, active, P, e_out,
+  eigh_density_kernel<NT, MINB, FAST_T><<<(unsigned)nmol, NT, smem, st>>>(S, mp, F, nheavy, nhydro, nocc, active, P, e_out,
                                                                   v_out, info, Vstore, warm, tol);
   SEQM_CHECK_LAUNCH("eigh_density_kernel");
   return SEQM_OK;
@@ -249,11 +268,15 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   else if (mp <= 32 && !g_force_block_jacobi)
     rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 32)
-    rc = launch_cfg<256, 7>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+    rc = launch_cfg<256, 7, false>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+  else if (mp <= 48 && (g_eigh_cfg & 1))
+    rc = launch_cfg<256, 4, true>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+  else if (mp <= 64 && (g_eigh_cfg & 2))
+    rc = launch_cfg<512, 2, true>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else if (mp <= 64)
-    rc = launch_cfg<512, 2>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+    rc = launch_cfg<512, 2, false>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else
-    rc = launch_cfg<1024, 1>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+    rc = launch_cfg<1024, 1, false>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   prof_mark("end", st);
   return rc;
 }
@@ -266,6 +289,7 @@ extern "C" {
 
 int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
 void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
+void seqm_eigh_block_config(int bits) { g_eigh_cfg = bits; }
 
 void seqm_eigh_tolerance(double tol) {
   g_eigh_tol = tol > 0.0 ? tol : 1.0e-24;
