@@ -140,8 +140,8 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
 void seqm_eigh_force_block(int on); /* test hook: shared-memory (CTA) Jacobi also for m <= 32 */
-void seqm_eigh_block_config(int bits); /* shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64 */
-void seqm_eigh_tolerance(double tol); /* Jacobi stopping rule: one final sweep once off^2 <= tol * total^2 (defaults: 1e-24 CTA kernel, 1e-18 warp kernel; tol <= 0 restores them) */
+void seqm_eigh_block_config(int bits); /* shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64; default 3 (measured 135 -> 118 ms on the m > 32 molecules of config 4, tools/exp_organics_big.py) */
+void seqm_eigh_tolerance(double tol); /* Jacobi stopping rule: one final sweep once off^2 <= tol * total^2 (default 1e-18 for both kernels; tol <= 0 restores it) */
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                       double* e_out, double* v_out, int32_t* info, void* stream);
@@ -228,6 +228,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
  *   E = sum_b gE[b]*Eelec_b + sum_p gNuc[p]*EnucAB_p ;  D == NULL: Eelec = 0.5 sum P.(H+F(P)),
  *   D != NULL (XL-BOMD): Eelec = sum D.F(P) - 0.5 (F(P)-H).P.
  *   out: grad_xij[P][3], grad_rij[P]  (dE/dxij, dE/drij; chained through the Parser by autograd) */
+void seqm_pair_grad_reverse(int on); /* heavy-heavy pairs: 1 (default) reverse-mode kernel, 0 forward-mode duals (comparison / test hook) */
 int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const double* xij, const double* rij,
                    int ngauss, const double* P, const double* D, const double* gE, const double* gNuc,
                    double* grad_xij, double* grad_rij, void* stream);

@@ -56,6 +56,8 @@ def lib():
         L.seqm_eigh_force_block.argtypes = [ctypes.c_int]
         L.seqm_eigh_force_block.restype = None
         L.seqm_eigh_tolerance.argtypes = [ctypes.c_double]
+        L.seqm_pair_grad_reverse.argtypes = [ctypes.c_int]
+        L.seqm_pair_grad_reverse.restype = None
         L.seqm_eigh_block_config.argtypes = [ctypes.c_int]
         L.seqm_eigh_block_config.restype = None
         L.seqm_scf_fused.argtypes = [ctypes.c_int]
@@ -102,7 +104,7 @@ def lib():
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
                             'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps',
-                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
+                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
                 fn.restype = ctypes.c_int
         if os.environ.get('SEQM_SCF_WARPS'):
             L.seqm_scf_warps(int(os.environ['SEQM_SCF_WARPS']))
@@ -118,7 +120,7 @@ EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
            'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
            'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
-           'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config']
+           'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse']
 
 
 def check(rc, what):

@@ -220,10 +220,10 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
   }
 }
 
-double g_eigh_tol = 1.0e-24;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel)
+double g_eigh_tol = 1.0e-18;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel; 1e-24 until r01q: one sweep more, same result to 1e-11 eV)
 double g_eigh_tol_warp = 1.0e-18; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
 double eigh_tolerance() { return g_eigh_tol_warp; }
-int g_eigh_cfg = 0;      // experiment hook (seqm_eigh_block_config): bit 0: 256-thread CTAs + FP32 tangent for 32 < m <= 48, bit 1: FP32 tangent for m <= 64
+int g_eigh_cfg = 3;      // variant hook (seqm_eigh_block_config): bit 0: 256-thread CTAs + FP32 tangent for 32 < m <= 48, bit 1: FP32 tangent for m <= 64
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {
@@ -292,7 +292,7 @@ void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
 void seqm_eigh_block_config(int bits) { g_eigh_cfg = bits; }
 
 void seqm_eigh_tolerance(double tol) {
-  g_eigh_tol = tol > 0.0 ? tol : 1.0e-24;
+  g_eigh_tol = tol > 0.0 ? tol : 1.0e-18;
   g_eigh_tol_warp = tol > 0.0 ? tol : 1.0e-18;
 }
 

@@ -387,6 +387,137 @@ pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double
 }
 
 
+
+static int g_pair_grad_reverse = 1;      // 0: forward-mode kernel for heavy-heavy pairs too (test / comparison hook)
+
+// ---------------------------------------------------------------------------------------------
+// K4 for heavy-heavy pairs, reverse mode (replaces pair_grad_kernel<XX>, which pushed four tangents through the
+// integrals AND the rotation with the 100-element upstream in registers: 7.9 KB of spills per thread).
+//   * the upstream G[10][10] of the pair lives in shared memory, element-major (conflict-free, one column per thread)
+//   * local integrals with ONE tangent (d/dr, Dual<1>)
+//   * rotate_xx_adjoint (pair_math.cuh): one pass over the rows of G in plain doubles gives dE/dr and the adjoint of
+//     the rotation matrix; the three tangents of the local frame turn that into dE/dx
+//   * overlap (four tangents, small) and core repulsion (one tangent) as before
+// ---------------------------------------------------------------------------------------------
+constexpr int PGX_NT = 32;
+
+struct SmemG {
+  const double* g;      // this thread's column: element e at g[e * PGX_NT]
+  __device__ __forceinline__ double operator()(int k, int l) const { return g[(k * 10 + l) * PGX_NT]; }
+};
+
+__global__ void __launch_bounds__(PGX_NT)
+pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                    const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                    const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
+                    double* __restrict__ gx, double* __restrict__ gr) {
+  __shared__ double Gs[100 * PGX_NT];
+  const int slot = blockIdx.x * PGX_NT + threadIdx.x;
+  if (slot >= t.ncls[SEQM_CLS_XX]) return;
+  const int p = t.cls_pairs[SEQM_CLS_XX][slot];
+  const int i = t.idxi[p], j = t.idxj[p];
+  const AtomPar& a = ap[i];
+  const AtomPar& b = ap[j];
+  const int S = (int)t.molsize;
+  const size_t n4 = (size_t)4 * S;
+  const int mol = t.atom_mol[i];
+  const int si = t.atom_slot[i], sj = t.atom_slot[j];
+  const double* Pm = P + (size_t)mol * n4 * n4;
+  const double* Dmm = Dm ? Dm + (size_t)mol * n4 * n4 : nullptr;
+  double* Gt = Gs + threadIdx.x;
+  double eov[4] = {0.0, 0.0, 0.0, 0.0};      // overlap part of dE/d(x1, x2, x3, r)
+  {
+    double pA[10], pB[10], qA[10], qB[10], xA[10], xB[10];
+    load_diag_packed(Pm, n4, si, pA);
+    load_diag_packed(Pm, n4, sj, pB);
+    if (Dmm) {
+      load_diag_packed(Dmm, n4, si, xA);
+      load_diag_packed(Dmm, n4, sj, xB);
+#pragma unroll
+      for (int k = 0; k < 10; ++k) { qA[k] = xA[k] - 0.5 * pA[k]; qB[k] = xB[k] - 0.5 * pB[k]; }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 10; ++k) { xA[k] = pA[k]; xB[k] = pB[k]; qA[k] = 0.5 * pA[k]; qB[k] = 0.5 * pB[k]; }
+    }
+    double Pab[4][4], Qab[4][4];
+#pragma unroll
+    for (int mu = 0; mu < 4; ++mu)
+#pragma unroll
+      for (int nu = 0; nu < 4; ++nu) {
+        const size_t off = ((size_t)4 * si + mu) * n4 + 4 * sj + nu;
+        const double pv = Pm[off];
+        Pab[mu][nu] = pv;
+        Qab[mu][nu] = Dmm ? Dmm[off] - 0.5 * pv : 0.5 * pv;
+      }
+    // upstream on the integrals, one element at a time: Coulomb, exchange (every ordering of the two index pairs),
+    // and the core-electron attraction terms that ride on the (mu nu|ss) / (ss|la sg) integrals
+#pragma unroll
+    for (int mu = 0; mu < 4; ++mu)
+#pragma unroll
+      for (int nu = 0; nu <= mu; ++nu) {
+        const int k = IND(mu, nu);
+#pragma unroll
+        for (int la = 0; la < 4; ++la)
+#pragma unroll
+          for (int sg = 0; sg <= la; ++sg) {
+            const int l = IND(la, sg);
+            double g = qA[k] * pB[l] + pA[k] * qB[l] - Qab[mu][la] * Pab[nu][sg];
+            if (la != sg) g -= Qab[mu][sg] * Pab[nu][la];
+            if (mu != nu) {
+              g -= Qab[nu][la] * Pab[mu][sg];
+              if (la != sg) g -= Qab[nu][sg] * Pab[mu][la];
+            }
+            if (l == 0) g -= b.tore * xA[k];
+            if (k == 0) g -= a.tore * xB[l];
+            Gt[(k * 10 + l) * PGX_NT] = g;
+          }
+      }
+  }
+  {
+    // overlap part: dE/dM block = 2 X_AB (X = P, or D in the XL-BOMD energy), M = overlap * mean beta
+    if (rij[p] <= SEQM_OVERLAP_CUTOFF) {
+      const double* Xm = Dmm ? Dmm : Pm;
+      D4 x[3], r;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { x[c] = D4(xij[3 * p + c]); x[c].d[c] = 1.0; }
+      r = D4(rij[p]);
+      r.d[3] = 1.0;
+      D4 di[16];
+      overlap_block(SEQM_CLS_XX, x, r, a, b, di);
+#pragma unroll
+      for (int mu = 0; mu < 4; ++mu)
+#pragma unroll
+        for (int nu = 0; nu < 4; ++nu) {
+          const double f = Xm[((size_t)4 * si + mu) * n4 + 4 * sj + nu] * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp));
+#pragma unroll
+          for (int c = 0; c < 4; ++c) eov[c] += f * di[mu * 4 + nu].d[c];
+        }
+    }
+  }
+  typedef Dual<1> D1;
+  D1 r1(rij[p]);
+  r1.d[0] = 1.0;
+  double ri[22], dri[22];
+  {
+    D1 ri1[22];
+    repp_xx(r1, a.mp, b.mp, ri1);
+#pragma unroll
+    for (int q = 0; q < 22; ++q) { ri[q] = ri1[q].v; dri[q] = ri1[q].d[0]; }
+  }
+  const double xv[3] = {xij[3 * p], xij[3 * p + 1], xij[3 * p + 2]};
+  double grot[3], grr;
+  rotate_xx_adjoint(ri, dri, xv, SmemG{Gt}, grot, grr);
+  D1 gam(ri[0]);
+  gam.d[0] = dri[0];
+  const D1 en = core_repulsion(t.Z[i], t.Z[j], r1, gam, a, b, ngauss);
+  const double ge = gE ? gE[mol] : 1.0;
+  const double gn = gNuc ? gNuc[p] : 1.0;
+  gx[3 * p + 0] = ge * (grot[0] + eov[0]);
+  gx[3 * p + 1] = ge * (grot[1] + eov[1]);
+  gx[3 * p + 2] = ge * (grot[2] + eov[2]);
+  gr[p] = ge * (grr + eov[3]) + gn * en.d[0];
+}
+
 // ---------------------------------------------------------------------------------------------
 // Pair geometry on the device (the arithmetic of the reference Parser, basics.py:91-108) and its adjoint:
 //   d = R_j - R_i, dist = sqrt(d.d) (1e-4 A^2 if zero), xij = d/dist, rij = dist * lcf
@@ -552,7 +683,10 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
   cudaStream_t st = (cudaStream_t)stream;
   const AtomPar* ap = (const AtomPar*)atompar;
   prof_mark("pair_grad", st);
-  if (t.ncls[2] > 0) {
+  if (t.ncls[2] > 0 && g_pair_grad_reverse) {
+    pair_grad_xx_kernel<<<cdiv(t.ncls[2], PGX_NT), PGX_NT, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
+    SEQM_CHECK_LAUNCH("pair_grad_xx_kernel");
+  } else if (t.ncls[2] > 0) {
     pair_grad_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
     SEQM_CHECK_LAUNCH("pair_grad_kernel<XX>");
   }
@@ -567,6 +701,8 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
   prof_mark("end", st);
   return SEQM_OK;
 }
+
+void seqm_pair_grad_reverse(int on) { g_pair_grad_reverse = on; }
 
 int seqm_pair_geometry(const seqm_topology_t* topo, const double* R, double lcf, double* xij, double* rij,
                        void* stream) {

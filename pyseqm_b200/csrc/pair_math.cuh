@@ -114,6 +114,133 @@ SEQM_HD void rotate_xx(const S* ri, const S R[3][3], Sink& sink) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Reverse-mode adjoint of rotate_xx for the force kernel.  With w = T L T^T, T = diag(1, R, Tq(R)) and an upstream
+// G = dE/dw, the energy E = sum_kl G_kl w_kl has
+//   dE/dT_ka = (L a1_k)_a + (L^T a2_k)_a,   a1_k,b = sum_l G_kl T_lb,  a2_k,b = sum_l G_lk T_lb
+//   dE/dr    = sum_k sum_a T_ka (L' a1_k)_a                       (L' = dL/dr: the local integrals' r derivative)
+// so one pass over the ten rows k, in plain doubles, yields dE/dr and the 3 x 3 adjoint Y = dE/dR; dE/dx follows
+// from the tangents of local_frame (Dual<3>).  L is the local-frame integral matrix, i.e. rotate_xx with R = identity;
+// apply_L / apply_LT below write its sparsity out (local packed index: 0 ss | 1,3,6 p_sigma s, p_pi s, p_pi' s |
+// 2,4,5,7,8,9 the p p products in SEQM_PP order).
+// ---------------------------------------------------------------------------------------------
+SEQM_HD void apply_L(const double* ri, const double* v, double* o) {      // o_a = sum_b L_ab v_b
+  const double v25 = v[5] + v[9];
+  o[0] = ri[0] * v[0] + ri[4] * v[1] + ri[10] * v[2] + ri[11] * v25;
+  o[1] = ri[1] * v[0] + ri[5] * v[1] + ri[12] * v[2] + ri[13] * v25;
+  o[3] = ri[6] * v[3] + ri[14] * v[4];
+  o[6] = ri[6] * v[6] + ri[14] * v[7];
+  o[2] = ri[2] * v[0] + ri[7] * v[1] + ri[15] * v[2] + ri[17] * v25;
+  o[4] = ri[9] * v[3] + ri[19] * v[4];
+  o[5] = ri[3] * v[0] + ri[8] * v[1] + ri[16] * v[2] + ri[18] * v[5] + ri[20] * v[9];
+  o[7] = ri[9] * v[6] + ri[19] * v[7];
+  o[8] = ri[21] * v[8];
+  o[9] = ri[3] * v[0] + ri[8] * v[1] + ri[16] * v[2] + ri[20] * v[5] + ri[18] * v[9];
+}
+SEQM_HD void apply_LT(const double* ri, const double* v, double* o) {     // o_a = sum_b L_ba v_b
+  const double v25 = v[5] + v[9];
+  o[0] = ri[0] * v[0] + ri[1] * v[1] + ri[2] * v[2] + ri[3] * v25;
+  o[1] = ri[4] * v[0] + ri[5] * v[1] + ri[7] * v[2] + ri[8] * v25;
+  o[3] = ri[6] * v[3] + ri[9] * v[4];
+  o[6] = ri[6] * v[6] + ri[9] * v[7];
+  o[2] = ri[10] * v[0] + ri[12] * v[1] + ri[15] * v[2] + ri[16] * v25;
+  o[4] = ri[14] * v[3] + ri[19] * v[4];
+  o[5] = ri[11] * v[0] + ri[13] * v[1] + ri[17] * v[2] + ri[18] * v[5] + ri[20] * v[9];
+  o[7] = ri[14] * v[6] + ri[19] * v[7];
+  o[8] = ri[21] * v[8];
+  o[9] = ri[11] * v[0] + ri[13] * v[1] + ri[17] * v[2] + ri[20] * v[5] + ri[18] * v[9];
+}
+
+// local-frame images of row k and column k of G:  a1_b = sum_l G(k,l) T_lb,  a2_b = sum_l G(l,k) T_lb
+template <class GFun>
+SEQM_HD void g_images(const GFun& G, int k, const double R[3][3], const double Tq[6][6], double* a1, double* a2) {
+  a1[0] = G(k, 0);
+  a2[0] = G(0, k);
+  double g1[3], g2[3];
+#pragma unroll
+  for (int m = 0; m < 3; ++m) { g1[m] = G(k, SEQM_PS(m)); g2[m] = G(SEQM_PS(m), k); }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    a1[SEQM_PS(a)] = g1[0] * R[0][a] + g1[1] * R[1][a] + g1[2] * R[2][a];
+    a2[SEQM_PS(a)] = g2[0] * R[0][a] + g2[1] * R[1][a] + g2[2] * R[2][a];
+  }
+  double h1[6], h2[6];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) { h1[q] = G(k, SEQM_PP(q)); h2[q] = G(SEQM_PP(q), k); }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) { s1 += h1[q] * Tq[q][c]; s2 += h2[q] * Tq[q][c]; }
+    a1[SEQM_PP(c)] = s1;
+    a2[SEQM_PP(c)] = s2;
+  }
+}
+
+// G(k, l) -> upstream dE/dw[k][l];  ri, dri: local integrals and their r derivative;  xij: unit vector
+// out: gx[3] = dE/dxij, gr = dE/drij (integral part only)
+template <class GFun>
+SEQM_HD void rotate_xx_adjoint(const double* ri, const double* dri, const double* xij, const GFun& G, double* gx,
+                               double& gr) {
+  double R[3][3], Tq[6][6], Y[3][3];
+  local_frame(xij, R);
+#pragma unroll
+  for (int m = 0; m < 3; ++m)
+#pragma unroll
+    for (int a = 0; a < 3; ++a) Y[m][a] = 0.0;
+  build_tq(R, Tq);
+  double acc_r = 0.0;
+  double a1[10], a2[10], z1[10], z2[10], zr[10];
+  {      // k = 0 (ss): T_00 = 1 carries no geometry
+    g_images(G, 0, R, Tq, a1, a2);
+    apply_L(dri, a1, zr);
+    acc_r += zr[0];
+  }
+#pragma unroll
+  for (int m = 0; m < 3; ++m) {      // rows (p_m s): T = R[m][.]
+    g_images(G, SEQM_PS(m), R, Tq, a1, a2);
+    apply_L(ri, a1, z1);
+    apply_LT(ri, a2, z2);
+    apply_L(dri, a1, zr);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      Y[m][a] += z1[SEQM_PS(a)] + z2[SEQM_PS(a)];
+      acc_r += R[m][a] * zr[SEQM_PS(a)];
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 6; ++q) {      // rows (p_m p_n): T = Tq[q][.], Tq[q][(a,b)] = R[m][a]R[n][b] + (a != b) R[m][b]R[n][a]
+    g_images(G, SEQM_PP(q), R, Tq, a1, a2);
+    apply_L(ri, a1, z1);
+    apply_LT(ri, a2, z2);
+    apply_L(dri, a1, zr);
+    const int m = SEQM_QM(q), n = SEQM_QN(q);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+      const int a = SEQM_QM(c), b = SEQM_QN(c);
+      const double zc = z1[SEQM_PP(c)] + z2[SEQM_PP(c)];
+      acc_r += Tq[q][c] * zr[SEQM_PP(c)];
+      Y[m][a] += zc * R[n][b];
+      Y[n][b] += zc * R[m][a];
+      if (a != b) { Y[m][b] += zc * R[n][a]; Y[n][a] += zc * R[m][b]; }
+    }
+  }
+  gr = acc_r;
+  Dual<3> x3[3], R3[3][3];      // tangents of the frame (same branches as the plain evaluation above)
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { x3[c] = Dual<3>(xij[c]); x3[c].d[c] = 1.0; }
+  local_frame(x3, R3);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    double s = 0.0;
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+      for (int a = 0; a < 3; ++a) s += Y[m][a] * R3[m][a].d[c];
+    gx[c] = s;
+  }
+}
+
 // heavy-hydrogen pair: the ten (mu nu | s s) integrals, sink(k, 0, value)
 template <class S, class Sink>
 SEQM_HD void rotate_xh(const S* ri, const S R[3][3], Sink& sink) {

@@ -90,4 +90,18 @@ void hc_pair_dual(int ni, int nj, const double* xv, double rv, const double* apa
   enuc[0] = e.v;
   for (int c = 0; c < 4; ++c) enuc[1 + c] = e.d[c];
 }
+
+// reverse-mode adjoint of the heavy-heavy rotation (rotate_xx_adjoint): out[4] = dE/dx1, dx2, dx3, dr for E = sum G.w
+void hc_rotate_xx_adjoint(const double* x, double rv, const double* apar, const double* bpar, const double* G, double* out) {
+  const AtomPar& a = *(const AtomPar*)apar;
+  const AtomPar& b = *(const AtomPar*)bpar;
+  Dual<1> r(rv);
+  r.d[0] = 1.0;
+  Dual<1> ri1[22];
+  repp_xx(r, a.mp, b.mp, ri1);
+  double ri[22], dri[22];
+  for (int q = 0; q < 22; ++q) { ri[q] = ri1[q].v; dri[q] = ri1[q].d[0]; }
+  auto g = [G](int k, int l) { return G[k * 10 + l]; };
+  rotate_xx_adjoint(ri, dri, x, g, out, out[3]);
+}
 }

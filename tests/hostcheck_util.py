@@ -55,3 +55,11 @@ def pair_dual(ni, nj, x, r, apar, bpar, ngauss):
     x = np.ascontiguousarray(x, dtype=np.float64)
     lib().hc_pair_dual(int(ni), int(nj), _p(x), ctypes.c_double(r), _p(apar), _p(bpar), int(ngauss), _p(w), _p(di), _p(e))
     return w.reshape(10, 10, 5), di.reshape(4, 4, 5), e
+
+
+def rotate_xx_adjoint(x, r, apar, bpar, G):
+    out = np.zeros(4)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    G = np.ascontiguousarray(G, dtype=np.float64)
+    lib().hc_rotate_xx_adjoint(_p(x), ctypes.c_double(r), _p(apar), _p(bpar), _p(G), _p(out))
+    return out

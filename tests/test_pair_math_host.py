@@ -92,3 +92,25 @@ def test_pair_values_and_derivatives(method, aligned):
         g = float(Ge[p]) * ed[1:]
         ref = np.concatenate([gx_e[p].numpy(), [float(gr_e[p])]])
         assert np.abs(g - ref).max() < 1e-10 * max(1.0, np.abs(ref).max()), ('enuc', p, g, ref)
+
+
+@pytest.mark.parametrize('aligned', [False, True])
+def test_rotate_xx_adjoint_matches_forward_duals(aligned):
+    """rotate_xx_adjoint (reverse mode, what pair_grad_xx_kernel runs) against the forward-mode dual derivative of the
+    same rotation, heavy-heavy pairs, random upstream"""
+    ni, nj, xij, rij, tab = _pairs_case('PM3', 11, aligned)
+    Zflat = torch.stack((ni, nj), dim=1).reshape(-1)
+    apars, par, _ = _atompars(tab, 'PM3', Zflat.tolist())
+    rng = np.random.RandomState(5)
+    checked = 0
+    for p in range(ni.shape[0]):
+        if int(ni[p]) <= 1 or int(nj[p]) <= 1:
+            continue
+        a, b = apars[2 * p], apars[2 * p + 1]
+        G = rng.standard_normal((10, 10))
+        wd, _, _ = hc.pair_dual(int(ni[p]), int(nj[p]), xij[p].numpy(), float(rij[p]), a, b, 2)
+        ref = np.einsum('kl,klq->q', G, wd[..., 1:])
+        got = hc.rotate_xx_adjoint(xij[p].numpy(), float(rij[p]), a, b, G)
+        assert np.abs(got - ref).max() < 1e-12 * max(1.0, np.abs(ref).max()), (p, got, ref)
+        checked += 1
+    assert checked >= 6
