@@ -158,7 +158,9 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
           const double b10 = sa * a00 + ca * a10, b11 = sa * a01 + ca * a11;
           double c00 = cb * b00 - sb * b01, c01 = sb * b00 + cb * b01;            // columns: blk J_b
           double c10 = cb * b10 - sb * b11, c11 = sb * b10 + cb * b11;
-          if (ka == kb) { c01 = 0.0; c10 = 0.0; }
+          // exact tangent: the pivot is annihilated by construction; FP32 tangent: keep the (tiny) rotated value, the
+          // transformation must stay a similarity transform of what is stored
+          if (ka == kb) { if (FAST_T) { c01 = c10 = 0.5 * (c01 + c10); } else { c01 = 0.0; c10 = 0.0; } }
           A[pa * ld + pb] = c00; A[pa * ld + qb] = c01; A[qa * ld + pb] = c10; A[qa * ld + qb] = c11;
         } else {
           const int t2 = task - nblk;
