@@ -288,11 +288,17 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     tot = warp_sum(tot);
     if (off == 0.0 || last) break;
     if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
+    // the schedule entries of the next two rounds are fetched while the current two run (their shared-memory
+    // latency sat on the critical path of every round: ncu source view, r01p)
+    unsigned t0 = TAB[lane], t1 = TAB[32 + lane];
 #pragma unroll 1
     for (int r = 0; r < N; r += 2) {
-      const unsigned t0 = TAB[r * 32 + lane], t1 = TAB[(r + 1) * 32 + lane];
+      const int rn = (r + 2 < N) ? r + 2 : 0;
+      const unsigned n0 = TAB[rn * 32 + lane], n1 = TAB[(rn + 1) * 32 + lane];
       jacobi_round<N, 0>(a, v, S0, S1, CS, DSC, t0, sigma, lane, rowoff, on, dmy, idmy);
       jacobi_round<N, 1>(a, v, S1, S0, CS, DSC, t1, sigma, lane, rowoff, on, dmy, idmy);
+      t0 = n0;
+      t1 = n1;
     }
     sigma ^= 1;
     renormalise<N>(a, v, S0, DSC, sigma, lane, rowoff, on, dmy, idmy);
