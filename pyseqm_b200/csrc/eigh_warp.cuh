@@ -89,8 +89,8 @@ __device__ __forceinline__ double rsqrt_unit(double q) {
 template <int N, int PAR>
 __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], const double* __restrict__ Sr,
                                              double* __restrict__ Sw, double* __restrict__ CS,
-                                             double2* __restrict__ DSC, unsigned tab, int sigma, int lane, int rowoff,
-                                             bool on, double& dmy, double& idmy) {
+                                             double2* __restrict__ DSC, unsigned tab, unsigned tab_next, int sigma,
+                                             int lane, int rowoff, bool on, double& dmy, double& idmy) {
   constexpr int LD = WarpLd<N>::value;
   constexpr int NPAIR = PAR ? N / 2 - 1 : N / 2;
   SEQM_TICK(0);
@@ -99,14 +99,20 @@ __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], con
   const bool left = (((tab >> 10) & 1) != sigma) && act;
   const int L0 = (tab >> 5) & 31;
   const int L = (sigma && on) ? N - 2 - L0 : L0;
-  const int prow = partner * LD;
-  const double x0 = Sr[rowoff + L], x1 = Sr[rowoff + L + 1];
-  const double y0 = Sr[prow + L], y1 = Sr[prow + L + 1];
+  // SLOT SCHEME: in the buffer of round r the row of lane i sits in the slot of its partner of that round, i.e.
+  // slot `lane` holds the PARTNER's row.  The 15 LDS.128 of the partner row (the critical path of the round) then
+  // read consecutive slots from consecutive lanes - conflict free; the scattered side is the store of the updated
+  // row into the slot of the NEXT round's partner, which nothing waits for (ncu r01p: 1.7x excess wavefronts on
+  // these loads, short_scoreboard the top stall).
+  const int orow = partner * LD;            // own row (two scalars needed)
+  const int wrow = (int)(tab_next & 31) * LD;
+  const double x0 = Sr[orow + L], x1 = Sr[orow + L + 1];
+  const double y0 = Sr[rowoff + L], y1 = Sr[rowoff + L + 1];
   const double2 dpn = DSC[partner];
   double b[N];
 #pragma unroll
   for (int jj = 0; jj < N / 2; ++jj) {
-    const double2 t = *reinterpret_cast<const double2*>(&Sr[prow + 2 * jj]);
+    const double2 t = *reinterpret_cast<const double2*>(&Sr[rowoff + 2 * jj]);
     b[2 * jj] = t.x;
     b[2 * jj + 1] = t.y;
   }
@@ -159,7 +165,7 @@ __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], con
   if (on) {
 #pragma unroll
     for (int jj = 0; jj < N / 2; ++jj)
-      *reinterpret_cast<double2*>(&Sw[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
+      *reinterpret_cast<double2*>(&Sw[wrow + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
   }
   SEQM_TICK(5);
   __syncwarp();
@@ -170,7 +176,7 @@ __device__ __forceinline__ void jacobi_round(double (&a)[N], double (&v)[N], con
 // sigma = arrangement after the sweep (1: column id N-1-j at position j)
 template <int N>
 __device__ __forceinline__ void renormalise(double (&a)[N], double (&v)[N], double* __restrict__ S,
-                                            double2* __restrict__ DSC, int sigma, int lane, int rowoff, bool on,
+                                            double2* __restrict__ DSC, int sigma, int lane, int slotoff, bool on,
                                             double& dmy, double& idmy) {
 #pragma unroll
   for (int j = 0; j < N; ++j) {
@@ -185,7 +191,7 @@ __device__ __forceinline__ void renormalise(double (&a)[N], double (&v)[N], doub
     DSC[lane] = make_double2(1.0, 1.0);
 #pragma unroll
     for (int jj = 0; jj < N / 2; ++jj)
-      *reinterpret_cast<double2*>(&S[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
+      *reinterpret_cast<double2*>(&S[slotoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
   }
   __syncwarp();
 }
@@ -255,18 +261,20 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
       }
     }
     __syncwarp();
-    if (on) {
-#pragma unroll
-      for (int jj = 0; jj < N / 2; ++jj)
-        *reinterpret_cast<double2*>(&S0[rowoff + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
-    }
-    __syncwarp();
   } else {
 #pragma unroll
     for (int j = 0; j < N; ++j) v[j] = (j == lane) ? 1.0 : 0.0;
   }
+  // publish the rows in the slot arrangement of round 0 (slot of the round-0 partner; same in mirrored sweeps)
+  const int slot0 = on ? (int)(TAB[lane] & 31) * LD : 0;
+  if (on) {
+#pragma unroll
+    for (int jj = 0; jj < N / 2; ++jj)
+      *reinterpret_cast<double2*>(&S0[slot0 + 2 * jj]) = make_double2(a[2 * jj], a[2 * jj + 1]);
+  }
+  __syncwarp();
   SEQM_PHASE(7);
-  // S0 holds the rows of the current A
+  // S0 holds the rows of the current A (slot arrangement of round 0)
   double2* DSC = reinterpret_cast<double2*>(CS + N);      // [N] (d, 1/d) per column id
   if (on) DSC[lane] = make_double2(1.0, 1.0);
   double dmy = 1.0, idmy = 1.0;
@@ -295,13 +303,13 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     for (int r = 0; r < N; r += 2) {
       const int rn = (r + 2 < N) ? r + 2 : 0;
       const unsigned n0 = TAB[rn * 32 + lane], n1 = TAB[(rn + 1) * 32 + lane];
-      jacobi_round<N, 0>(a, v, S0, S1, CS, DSC, t0, sigma, lane, rowoff, on, dmy, idmy);
-      jacobi_round<N, 1>(a, v, S1, S0, CS, DSC, t1, sigma, lane, rowoff, on, dmy, idmy);
+      jacobi_round<N, 0>(a, v, S0, S1, CS, DSC, t0, t1, sigma, lane, rowoff, on, dmy, idmy);
+      jacobi_round<N, 1>(a, v, S1, S0, CS, DSC, t1, n0, sigma, lane, rowoff, on, dmy, idmy);
       t0 = n0;
       t1 = n1;
     }
     sigma ^= 1;
-    renormalise<N>(a, v, S0, DSC, sigma, lane, rowoff, on, dmy, idmy);
+    renormalise<N>(a, v, S0, DSC, sigma, lane, slot0, on, dmy, idmy);
   }
   SEQM_PHASE(8);
   const int colid = on ? (sigma ? N - 1 - lane : lane) : 0;      // column id at position `lane`
@@ -316,7 +324,7 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
   }
 
   // eigenvalue at POSITION `lane`: the diagonal element of the row that owns that column
-  const double e = on ? S0[colid * LD + lane] : 0.0;
+  const double e = on ? S0[(int)(TAB[colid] & 31) * LD + lane] : 0.0;      // row colid sits in its round-0 partner's slot
   // positions that belong to the padding carry unit vectors on rows >= m
   unsigned dummy = 0u;
 #pragma unroll
