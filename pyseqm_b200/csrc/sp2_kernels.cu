@@ -58,10 +58,6 @@ struct SeqmComm {
   double* bar;                     // [2 * nranks] doubles: barrier payload
 };
 
-struct Sp2State {      // per molecule
-  double tr, e0, e1, occ;
-  int live, niter, square, pad;
-};
 
 __device__ __forceinline__ int pk2pad(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
 
@@ -291,6 +287,9 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
     }
     asm volatile("cp.async.commit_group;\n" ::);
   };
+  // diagonal tiles: the two 16 x 32 warp tiles strictly below the diagonal are not multiplied - the epilogue mirrors
+  // the upper half (bit-identical: X is exactly symmetric, so both halves are the same sums in the same order)
+  const bool below = (ti == tj) && (wm >= wn + 32);
   const int nk = (nn + SBK - 1) / SBK;
   load_tiles(0, 0);
   for (int kt = 0; kt < nk; ++kt) {
@@ -304,17 +303,19 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
     __syncthreads();
     const double* as = As0 + buf * SBM * SLDA;
     const double* bs = Bs0 + buf * SBK * SLDB;
+    if (!below) {
 #pragma unroll
-    for (int kk = 0; kk < SBK; kk += 4) {
-      double af[2], bf[4];
+      for (int kk = 0; kk < SBK; kk += 4) {
+        double af[2], bf[4];
 #pragma unroll
-      for (int i = 0; i < 2; ++i) af[i] = as[(wm + i * 8 + g) * SLDA + kk + t];
+        for (int i = 0; i < 2; ++i) af[i] = as[(wm + i * 8 + g) * SLDA + kk + t];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) bf[j] = bs[(kk + t) * SLDB + wn + j * 8 + g];
+        for (int j = 0; j < 4; ++j) bf[j] = bs[(kk + t) * SLDB + wn + j * 8 + g];
 #pragma unroll
-      for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) s_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+          for (int j = 0; j < 4; ++j) s_dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+      }
     }
     __syncthreads();
   }
@@ -344,15 +345,16 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   for (int idx = tid; idx < SBM * SBM; idx += 256) {
     const int rl = idx >> 6, cl = idx & 63;
     const int r = m0 + rl, c = n0 + cl;
+    const bool mir = (ti == tj) && (rl > cl);
     if (SH) {
-      const double y = Ts[rl * SLDT + cl];          // zero outside the matrix
+      const double y = mir ? Ts[cl * SLDT + rl] : Ts[rl * SLDT + cl];          // zero outside the matrix
       for (int q = 0; q < peers.n; ++q) peers.p[q][myoff + idx] = y;      // NVLink stores for q != own rank
       pfr += y * y;
       if (ti == tj && rl == cl) ptr += y;
       continue;
     }
     if (r < nn && c < nn) {
-      const double y = Ts[rl * SLDT + cl];
+      const double y = mir ? Ts[cl * SLDT + rl] : Ts[rl * SLDT + cl];
       Xout[(size_t)r * ld + c] = y;
       pfr += y * y;
       if (ti == tj && rl == cl) ptr += y;
