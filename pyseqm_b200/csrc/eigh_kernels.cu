@@ -113,7 +113,8 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
         int p, q;
         if (tid == 0) { p = mp - 1; q = r; }
         else { p = (r + tid) % (mp - 1); q = (r - tid + mp - 1) % (mp - 1); }
-        if (p > q) { const int tmp = p; p = q; q = tmp; }
+        // (no ordering of p, q: p_k = r + k and q_k = r - k (mod mp - 1) stay consecutive over the pairs k, which is what
+        // makes the strided accesses of the update phase below bank-conflict free; the rotation formula is symmetric)
         const double apq = A[p * ld + q];
         double c = 1.0, s = 0.0;
         if (apq != 0.0) {
@@ -148,7 +149,10 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
       const int nblk = half * half;
       for (int task = tid; task < nblk + mp * half; task += NT) {
         if (task < nblk) {
-          const int ka = task / half, kb = task - ka * half;
+          // consecutive lanes take consecutive ka: rows pa = r + ka ascend and qa = r - ka descend by one, the row stride
+          // ld is odd, so the 16 doubles of a half-warp access fall into distinct bank pairs (ncu r01q: 39 % of the
+          // shared-memory wavefronts of the kb-fastest order were conflicts)
+          const int kb = task / half, ka = task - kb * half;
           const int2 ra = *reinterpret_cast<const int2*>(pq + 2 * ka), rb = *reinterpret_cast<const int2*>(pq + 2 * kb);
           const double2 ja = *reinterpret_cast<const double2*>(cs + 2 * ka), jb = *reinterpret_cast<const double2*>(cs + 2 * kb);
           const int pa = ra.x, qa = ra.y, pb = rb.x, qb = rb.y;
@@ -164,7 +168,7 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
           A[pa * ld + pb] = c00; A[pa * ld + qb] = c01; A[qa * ld + pb] = c10; A[qa * ld + qb] = c11;
         } else {
           const int t2 = task - nblk;
-          const int i = t2 / half, kb = t2 - i * half;
+          const int kb = t2 / mp, i = t2 - kb * mp;      // consecutive lanes: consecutive rows of V, same column pair
           const int2 rb = *reinterpret_cast<const int2*>(pq + 2 * kb);
           const double2 jb = *reinterpret_cast<const double2*>(cs + 2 * kb);
           const double v0 = V[i * ld + rb.x], v1 = V[i * ld + rb.y];
