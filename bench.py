@@ -648,9 +648,10 @@ def run_organics(args, rank, world, local_rank):
     const = Constants().to(dev)
     fm = Force(par).to(dev)
     bb = BucketedBatch(species)
+    workers = int(os.environ.get('SEQM_SWEEP_WORKERS', '6'))      # buckets run concurrently (threads + streams); 0: one after the other
 
     def step(x):
-        f, Etot, Hf, nc = bb.run(fm, const, x)
+        f, Etot, Hf, nc = bb.run(fm, const, x, workers=workers)
         if world > 1:
             gather_molecules(Etot, ntotal, world)
         return f, Etot, nc
@@ -745,7 +746,7 @@ def run_organics(args, rank, world, local_rank):
         "config": {"workload": "MNDO SCF+forces sweep, %d mixed organics of 5-30 atoms (2048 grown molecules x perturbed "
                                "copies), eigh, converger [2], scf_eps 1e-6, sharded by molecule over %d GPU(s) "
                                "(BASELINE.json configs[3])" % (ntotal, world),
-                   "molecules_per_gpu": nloc, "buckets_rank0": bb.summary(),
+                   "molecules_per_gpu": nloc, "buckets_rank0": bb.summary(), "concurrent_bucket_workers": workers,
                    "l2": "working set of a sweep (integrals + matrices of %d molecules) exceeds L2" % nloc,
                    "scf_not_converged": nfail},
         "e2e": {"value": ntotal / (e2e_ms / args.steps * 1e-3), "unit": "molecules/s",

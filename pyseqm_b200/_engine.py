@@ -7,6 +7,7 @@ Parser's index tensors, topology, per-atom parameters and records, the initial d
 energies) is computed once and reused while the same species tensor comes back (MD, geometry scans); per call
 only the pair geometry (one kernel, with a kernel adjoint) is recomputed.  It applies when the pair list cannot
 change with the coordinates (pair_outer_cutoff effectively infinite) and no per-call parameters are given."""
+import threading
 import time
 import warnings
 
@@ -19,6 +20,7 @@ _TOPO_CACHE = []      # small LRU of (key tensors, PairTopology)
 _TOPO_CACHE_SIZE = 4
 _PREP_CACHE = []
 _PREP_CACHE_SIZE = 4
+_PREP_LOCK = threading.Lock()      # BucketedBatch may drive several Force modules from worker threads
 ALL_PAIRS_CUTOFF = 1.0e6      # Angstrom: beyond any molecule, the pair list is the full a<b list
 
 
@@ -158,12 +160,14 @@ def prepared_for(const, parser, packpar, species, coordinates, method, learned_p
     if not (parser.outercutoff >= ALL_PAIRS_CUTOFF) or not species.is_cuda:
         return None
     key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method, id(packpar))
-    for k, prep in enumerate(_PREP_CACHE):
-        if prep.key == key:
-            if k:
-                _PREP_CACHE.insert(0, _PREP_CACHE.pop(k))
-            return prep
+    with _PREP_LOCK:
+        for k, prep in enumerate(_PREP_CACHE):
+            if prep.key == key:
+                if k:
+                    _PREP_CACHE.insert(0, _PREP_CACHE.pop(k))
+                return prep
     prep = Prepared(const, parser, packpar, species, coordinates, method)
-    _PREP_CACHE.insert(0, prep)
-    del _PREP_CACHE[_PREP_CACHE_SIZE:]
+    with _PREP_LOCK:
+        _PREP_CACHE.insert(0, prep)
+        del _PREP_CACHE[_PREP_CACHE_SIZE:]
     return prep

@@ -47,19 +47,49 @@ class BucketedBatch:
     def summary(self):
         return [(int(idx.numel()), int(sp.shape[1]), int(packed_sizes(sp).max())) for idx, sp in self.buckets]
 
-    def run(self, force_module, const, coordinates):
-        """-> force [B,S,3], Etot [B], Hf [B], notconverged [B] in the caller's molecule order"""
+    def run(self, force_module, const, coordinates, workers=0):
+        """-> force [B,S,3], Etot [B], Hf [B], notconverged [B] in the caller's molecule order.
+        workers > 0: the buckets run concurrently, one host thread, CUDA stream and `Force` module per bucket (the
+        SCF of the larger molecules synchronises its stream once per iteration, which leaves the GPU idle between
+        the launches of a small bucket; independent buckets fill those gaps).  The ctypes calls release the GIL."""
         dev = coordinates.device
         force = torch.zeros(self.nmol, self.molsize, 3, dtype=coordinates.dtype, device=dev)
         Etot = torch.zeros(self.nmol, dtype=coordinates.dtype, device=dev)
         Hf = torch.zeros_like(Etot)
         nc = torch.zeros(self.nmol, dtype=torch.bool, device=dev)
-        for idx, sp in self.buckets:
+        coords = coordinates.detach()
+
+        def one(k, fm):
+            idx, sp = self.buckets[k]
             S = sp.shape[1]
-            xyz = coordinates.detach()[idx][:, :S].contiguous()
-            out = force_module(const, xyz, sp)
-            force[idx, :S] = out[0]
-            Etot[idx] = out[2].detach()
-            Hf[idx] = out[3].detach()
-            nc[idx] = out[10]
+            out = fm(const, coords[idx][:, :S].contiguous(), sp)
+            return out[0], out[2].detach(), out[3].detach(), out[10]
+
+        if workers <= 0 or len(self.buckets) < 2:
+            results = [one(k, force_module) for k in range(len(self.buckets))]
+        else:
+            from concurrent.futures import ThreadPoolExecutor
+            if not hasattr(self, '_workers'):
+                self._workers = [(type(force_module)(force_module.seqm_parameters).to(dev), torch.cuda.Stream(device=dev))
+                                 for _ in self.buckets]
+            main = torch.cuda.current_stream(dev)
+
+            def job(k):
+                fm, stream = self._workers[k]
+                with torch.cuda.device(dev), torch.cuda.stream(stream):
+                    stream.wait_stream(main)
+                    res = one(k, fm)
+                stream.synchronize()
+                return res
+
+            # largest buckets first: they are the long poles
+            order = sorted(range(len(self.buckets)), key=lambda k: -self.buckets[k][0].numel() * self.buckets[k][1].shape[1] ** 2)
+            with ThreadPoolExecutor(max_workers=min(workers, len(order))) as pool:
+                futs = {k: pool.submit(job, k) for k in order}
+                results = [futs[k].result() for k in range(len(self.buckets))]
+        for (idx, sp), (f, e, h, c) in zip(self.buckets, results):
+            force[idx, :sp.shape[1]] = f
+            Etot[idx] = e
+            Hf[idx] = h
+            nc[idx] = c
         return force, Etot, Hf, nc

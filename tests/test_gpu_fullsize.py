@@ -210,6 +210,12 @@ def test_config4_bucketed_sweep_matches_plain_batch():
     assert float((Etot - plain[2].detach()).abs().max()) < 2e-6
     assert float((Hf - plain[3].detach()).abs().max()) < 2e-6
     assert float((f - plain[0]).abs().max()) < 2e-5
+    # buckets driven concurrently (one thread + stream + Force module per bucket): same numbers
+    f2, Etot2, Hf2, nc2 = bb.run(fm, const, coords, workers=4)
+    f3, Etot3, _, _ = bb.run(fm, const, coords, workers=4)          # second pass: cached species data, worker reuse
+    assert not bool(nc2.any())
+    assert float((Etot2 - Etot).abs().max()) < 1e-9 and float((f2 - f).abs().max()) < 1e-9
+    assert float((Etot3 - Etot).abs().max()) < 1e-9 and float((f3 - f).abs().max()) < 1e-9
     sel = torch.tensor([0, 17, 40, 95])
     ref = orc.run(torch.as_tensor(sp)[sel], torch.as_tensor(xyz)[sel], method='MNDO', scf_eps=1e-6, converger=(2, 0.0))
     assert float((Etot[sel.to(dev)].cpu() - ref['Etot']).abs().max()) < 1e-5
