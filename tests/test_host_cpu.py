@@ -93,3 +93,22 @@ def test_bucketed_batch_plan_covers_every_molecule_once():
         assert int(m.min()) > edges[k - 1] and int(m.max()) <= edges[k]
     sp2, xyz2 = synth.mixed_organics_sweep(100, seed=0, base=40)
     assert sp2.shape == (100, 30) and (sp2[40:80] == sp2[:40]).all() and not np.allclose(xyz2[40:80], xyz2[:40])
+
+
+def test_new_entry_points_reject_bad_arguments_without_a_gpu():
+    """argument checks of the sharded-SP2 / workspace entry points run before any CUDA call"""
+    import ctypes
+    from pyseqm_b200 import _lib
+    L = _lib.lib()
+    assert L.seqm_sp2_density_nccl(None, 0, 1, 4, 8, None, None, None, None, 1e-5, None, None, None, None, None) < 0
+    assert b'ranks' in L.seqm_last_error()
+    assert L.seqm_sp2_density_nccl(None, 2, 1, 4, 8, None, None, None, None, 1e-5, None, None, None, None, None) < 0
+    assert b'bad argument' in L.seqm_last_error()
+    h = ctypes.c_void_p()
+    assert L.seqm_nccl_comm_create(None, 0, 2, ctypes.byref(h)) < 0
+    assert L.seqm_nccl_comm_create(ctypes.create_string_buffer(128), 3, 2, ctypes.byref(h)) < 0
+    assert L.seqm_nccl_unique_id(None) < 0
+    # workspaces grow with the system and with the number of ranks' padding
+    assert L.seqm_sp2_nccl_workspace(1, 1500, 8) > L.seqm_sp2_workspace(1, 1500) > 2 * 6000 * 6000 * 8
+    assert L.seqm_elec_energy_workspace(1, 1500) == ((6000 * 6000 + 8191) // 8192) * 8
+    assert L.seqm_elec_energy_workspace(1024, 12) == 1024 * 8
