@@ -759,6 +759,13 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
     cudaEventRecord(cm->ready, st);
     cudaStreamWaitEvent(cm->side, cm->ready, 0);
   }
+  if (p2p) {
+    // entry barrier: a peer may still be unpacking the last step of the PREVIOUS call out of the record buffer
+    // this call's first launch is about to store into (cm->bar: [0, 2n) step barriers, [12n, 13n) this one)
+    double* eb = cm->bar + (size_t)12 * nranks;
+    const int r = api->AllGather(eb + myrank, eb, 1, NCCL_FLOAT64, cm->comm, st);
+    if (r) { set_error(std::string("ncclAllGather (entry barrier): ") + api->GetErrorString(r)); cudaFreeHost(hlive); return SEQM_ECUDA; }
+  }
   // two purification steps per host synchronisation: the second is a no-op (CTAs exit on the live flag) when the
   // first one finished every molecule
   for (int it = 0; it < 200 && rc == SEQM_OK; it += 2) {
