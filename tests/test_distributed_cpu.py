@@ -110,3 +110,51 @@ def test_sp2_tile_plan_world2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(r[3] for r in res) and res[0][2] == res[1][1]
+
+
+class _FakeForce:
+    """stands for pyseqm_b200.basics.Force on the CPU: per-molecule results that depend on the molecule only"""
+
+    def __call__(self, const, xyz, sp):
+        from pyseqm_b200.batching import packed_sizes
+        e = (xyz * (sp > 0).unsqueeze(2)).sum(dim=(1, 2)) + packed_sizes(sp).to(xyz.dtype)
+        out = [None] * 11
+        out[0], out[2], out[3], out[10] = -xyz, e, 2.0 * e, torch.zeros(sp.shape[0], dtype=torch.bool)
+        return tuple(out)
+
+
+def _sweep_worker(rank, world, port, nmol, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    import numpy as np
+    from pyseqm_b200 import synth
+    from pyseqm_b200.batching import BucketedBatch, packed_sizes
+    from pyseqm_b200.distributed import gather_molecules, shard_bounds
+    sp, xyz = synth.mixed_organics_sweep(nmol, seed=0, base=24)
+    species, coords = torch.as_tensor(sp), torch.as_tensor(xyz)
+    lo, hi = shard_bounds(nmol, world)[rank]
+    bb = BucketedBatch(species[lo:hi], max_chunk=8)
+    f, e, hf, nc = bb.run(_FakeForce(), None, coords[lo:hi])
+    e_all = gather_molecules(e, nmol)
+    want = (coords * (species > 0).unsqueeze(2)).sum(dim=(1, 2)) + packed_sizes(species).to(coords.dtype)
+    ok = bool(torch.allclose(e_all, want, rtol=0, atol=1e-12)) and bool(torch.equal(f, -coords[lo:hi] * (species[lo:hi] > 0).unsqueeze(2)))
+    q.put((rank, lo, hi, ok))
+    dist.destroy_process_group()
+
+
+def test_bucketed_sweep_sharded_world2_gloo():
+    """config 4's N > 1 host path: contiguous molecule shards, a size-bucketed sweep per rank, results scattered back
+    into shard order and gathered into the global order (world size 2, gloo, a CPU stand-in for Force)"""
+    world, nmol = 2, 61
+    port = _free_port()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sweep_worker, args=(r, world, port, nmol, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=180) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(r[3] for r in res) and res[0][2] == res[1][1] and res[1][2] == nmol
