@@ -6,7 +6,8 @@
 // which costs nothing because the rotated values are written to the exchanged registers.  After N rounds the
 // column order is reversed and every pair of columns has met exactly once (one sweep); all register indices
 // are compile-time constants.  The row half of the similarity transform needs the partner row: rows are
-// published in shared memory once per round (double buffered) and read back with 128-bit loads; the N/2
+// published in shared memory once per round (double buffered, each row in the slot of the lane that will need it
+// next - see jacobi_round) and read back with 128-bit loads; the N/2
 // rotation coefficients of a round travel through shared memory as well.  Rotations are applied in the scaled
 // (fast Givens) form, one FMA per element.  Per round and lane: 3N FP64 operations + ~40 for the rotation,
 // ~1.5N + 4 shared-memory instructions, two warp shuffles (position bookkeeping), two __syncwarp.
