@@ -8,8 +8,8 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..'))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', 'oracle'))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', '..'))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', '..', 'oracle'))
 torch.set_default_dtype(torch.float64)
 dev = torch.device('cuda:0')
 
@@ -58,7 +58,7 @@ def stage_scf(name, max_iter):
     from pyseqm_b200.basics import Force
     from pyseqm_b200.seqm_functions.constants import Constants
     from pyseqm_b200.seqm_functions import scf_loop
-    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', 'tests'))
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), '..'))
     import test_gpu_parity as T
     gg = T._load(name)
     sp = T._params(gg)
