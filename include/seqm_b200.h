@@ -8,12 +8,18 @@
  * (INTEGRATION.md shows the stub).
  *
  * Conventions
- *   - every pointer is a DEVICE pointer to caller-owned contiguous memory (PyTorch allocations);
- *     the library never allocates or frees device memory; scratch is passed in.
+ *   - every pointer is a DEVICE pointer to caller-owned contiguous memory (PyTorch allocations); scratch is
+ *     passed in (seqm_*_workspace).  The library itself allocates only (i) 512 bytes of page-locked host memory
+ *     per calling thread (the status word the host-driven loops read back) and (ii), for the multi-GPU SP2 form,
+ *     the peer-mapped record buffers of a communicator (seqm_nccl_comm_create .. seqm_nccl_comm_destroy).
  *   - all floating point data is fp64, index data is int32 unless noted (the int64 index tensors of
  *     the reference API are narrowed once per geometry by the host layer).
- *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*), do not synchronise unless
- *     documented, and keep no global mutable state.
+ *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*) and do not synchronise unless
+ *     documented.  Entry points may be called concurrently from several host threads on different streams
+ *     (the launch counter is atomic, the profiler's mark list is locked, error text is thread local).
+ *     Process-wide state is limited to the TEST / TUNING hooks marked "process-wide" below (Jacobi tolerance and
+ *     variant selection, fused-SCF switch, adjoint mode, SP2 sharding communicator): set them before the threads
+ *     start; everything a caller needs per call travels in the arguments (seqm_scf_options_t).
  *   - return value: 0 on success, negative seqm_status_t otherwise; seqm_last_error() gives the text
  *     (thread local).
  *
@@ -139,20 +145,28 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
  *   v_out[B][n][n] (may be NULL) eigenvectors in the reference's packed layout C[packed orbital][k];
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
-void seqm_eigh_force_block(int on); /* test hook: shared-memory (CTA) Jacobi also for m <= 32 */
-void seqm_eigh_block_config(int bits); /* shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64; default 3 (measured 135 -> 118 ms on the m > 32 molecules of config 4, tools/exp_organics_big.py) */
-void seqm_eigh_tolerance(double tol); /* Jacobi stopping rule: one final sweep once off^2 <= tol * total^2 (default 1e-18 for both kernels; tol <= 0 restores it) */
+void seqm_eigh_force_block(int on); /* process-wide test hook: shared-memory (CTA) Jacobi also for m <= 32 */
+void seqm_eigh_block_config(int bits); /* process-wide tuning hook: shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64; default 3 (measured 135 -> 118 ms on the m > 32 molecules of config 4, tools/exp_organics_big.py) */
+void seqm_eigh_tolerance(double tol); /* process-wide: Jacobi stopping rule, one final sweep once off^2 <= tol * total^2 (default 1e-16 for both kernels - r02a: 1e-14 fails the 1e-9 density check on one fixture, 1e-16 passes all and is 4.6 % faster than 1e-18; tol <= 0 restores it) */
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                       double* e_out, double* v_out, int32_t* info, void* stream);
 
 /* SP2() (reference SP2.py:3-72) on packed matrices with pack/unpack folded in.  Fpad[B][n][n] in,
  * D[B][n][n] out (= 2 X, padded layout).  work: seqm_sp2_workspace(...) bytes of scratch.
- * niter[B] (may be NULL) multiplications used.  Synchronises the stream (host reads a counter). */
+ * niter[B] (may be NULL) multiplications used.  Synchronises the stream: the host reads the per-step counters of
+ * live molecules, the first time after as many steps as the previous call needed (one synchronisation per call in a
+ * steady-state loop such as MD or the later SCF iterations), then every two steps.
+ * seqm_sp2_density_async: exactly `steps` (<= 64, rounded up to even) purification steps are enqueued, finished
+ * molecules are skipped by their CTAs; no host synchronisation or allocation, so the call can be captured in a CUDA
+ * graph; unfinished[0] (DEVICE int32) receives the number of molecules still live after the last step. */
 size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize);
 int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
                      double* D, int32_t* niter, void* work, void* stream);
+int seqm_sp2_density_async(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                           const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
+                           int32_t* niter, void* work, int steps, int32_t* unfinished, void* stream);
 
 /* Single large system (BASELINE.json configs[4]): the same purification with the 64x64 tiles of the upper block
  * triangle of X^2 SHARDED over the GPUs of one NCCL communicator (one process per GPU).  Rank g multiplies the
@@ -211,11 +225,6 @@ typedef struct {
                          stream reaches the end of the SCF */
 } seqm_scf_options_t;
 void seqm_scf_fused(int on);
-/* warps per molecule in the one-launch form and in the m <= 32 eigensolver: 1 (default) or 2 (columns of the
- * matrices split between the two warps of a 64-thread CTA; same arithmetic and schedule; measured slower on
- * config 2 - 2.60 ms against 2.26 ms per step - because the CTA barrier of every Jacobi round costs more than the
- * halved FMA work saves; kept as an experiment hook). */
-void seqm_scf_warps(int n);
 size_t seqm_scf_workspace(int64_t nmol, int64_t molsize, const seqm_scf_options_t* opt);
 int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const double* g_ss,
              const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,

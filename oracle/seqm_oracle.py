@@ -539,6 +539,21 @@ def density_eigh(F, nHeavy, nHydro, nocc, want_eig=False):
     return Pn
 
 
+def orbital_charges(v, nHeavy, nHydro, molsize):
+    """`charge` of scf_loop (scf_loop.py:788-800) from the eigenvector array of sym_eig_trunc, literally:
+    charge[b, :norb, :nX] = (v^2)[:norb, :4 nX].reshape(norb, 4, nX).sum(1), charge[b, :norb, nX:nX+nH] =
+    (v^2)[:norb, 4 nX:4 nX + nH]  (first index of v as stored by eigh, second index the eigenvector)."""
+    B = v.shape[0]
+    charge = torch.zeros(B, 4 * molsize, molsize, dtype=v.dtype)
+    v2 = v ** 2
+    for b in range(B):
+        nX, nH = int(nHeavy[b]), int(nHydro[b])
+        no = 4 * nX + nH
+        charge[b, :no, :nX] = v2[b, :no, :4 * nX].reshape(no, 4, nX).sum(dim=1)
+        charge[b, :no, nX:nX + nH] = v2[b, :no, 4 * nX:4 * nX + nH]
+    return charge
+
+
 def sp2_density(Fp, nocc, eps):
     """SP2 purification on packed matrices (SP2.py:3-72), fp64 branch.  Returns 2 X."""
     eps = min(max(eps, 1.0e-7), 1.0e-3)

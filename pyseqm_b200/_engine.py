@@ -20,7 +20,17 @@ _TOPO_CACHE = []      # small LRU of (key tensors, PairTopology)
 _TOPO_CACHE_SIZE = 4
 _PREP_CACHE = []
 _PREP_CACHE_SIZE = 4
-_PREP_LOCK = threading.Lock()      # BucketedBatch may drive several Force modules from worker threads
+_PREP_LOCK = threading.Lock()
+_TOKENS = iter(range(1, 1 << 62))      # identity of a Pack_Parameters instance in cache keys (id() can be recycled)
+
+
+def _token(obj):
+    t = getattr(obj, '_seqm_b200_token', None)
+    if t is None:
+        with _PREP_LOCK:
+            t = next(_TOKENS)
+        obj._seqm_b200_token = t
+    return t      # BucketedBatch may drive several Force modules from worker threads
 ALL_PAIRS_CUTOFF = 1.0e6      # Angstrom: beyond any molecule, the pair list is the full a<b list
 
 
@@ -102,6 +112,8 @@ def build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij,
         st.update(P=P, F=F, Eelec=E, notconverged=nc, niter=nit, nmol=int(nmol), max_iter=max_iter)
         if done is None:
             st['status'] = status          # resolved by resolve_status() once the stream has been synchronised
+            st['status_event'] = torch.cuda.Event()
+            st['status_event'].record()
             st['iterations'] = None
         else:
             st['iterations'] = done[0]
@@ -115,15 +127,26 @@ def _warn_unconverged(left, nmol, max_iter):
         warnings.warn("SCF for %d/%d molecules doesn't converge after %d iterations" % (left, nmol, max_iter))
 
 
-def resolve_status(st):
-    """finish a build() made with defer_status: wait for the stream, read {left, iterations}, warn like the reference"""
-    status = st.pop('status', None)
+def resolve_status(st, wait=True):
+    """finish a build() made with defer_status: wait for the SCF's status record (not for the whole stream), read
+    {left, iterations}, warn like the reference.  wait=False: only if the record has already arrived; returns whether
+    the status is resolved"""
+    status = st.get('status')
     if status is None:
-        return
-    torch.cuda.current_stream().synchronize()
+        return True
+    ev = st.get('status_event')
+    if ev is not None:
+        if not wait and not ev.query():
+            return False
+        ev.synchronize()
+    else:
+        torch.cuda.current_stream().synchronize()
+    st.pop('status', None)
+    st.pop('status_event', None)
     left, iters = int(status[0]), int(status[1])
     st['iterations'] = iters
     _warn_unconverged(left, st['nmol'], st['max_iter'])
+    return True
 
 
 def hcore_matrix(M, nmol, molsize):
@@ -141,7 +164,7 @@ class Prepared:
          self.pair_molid, self.ni, self.nj, self.idxi, self.idxj, _, _) = out
         self.species = species
         self.key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method,
-                    id(packpar))
+                    _token(packpar))
         self.parameters = packpar(self.Z, learned_params=dict())
         self.topo = PairTopology(self.nmol, self.molsize, self.Z, self.maskd, self.idxi, self.idxj, self.nHeavy,
                                  self.nHydro, self.nocc)
@@ -159,7 +182,7 @@ def prepared_for(const, parser, packpar, species, coordinates, method, learned_p
         return None
     if not (parser.outercutoff >= ALL_PAIRS_CUTOFF) or not species.is_cuda:
         return None
-    key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method, id(packpar))
+    key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method, _token(packpar))
     with _PREP_LOCK:
         for k, prep in enumerate(_PREP_CACHE):
             if prep.key == key:

@@ -62,8 +62,6 @@ def lib():
         L.seqm_eigh_block_config.restype = None
         L.seqm_scf_fused.argtypes = [ctypes.c_int]
         L.seqm_scf_fused.restype = None
-        L.seqm_scf_warps.argtypes = [ctypes.c_int]
-        L.seqm_scf_warps.restype = None
         L.seqm_eigh_tolerance.restype = None
         L.seqm_sp2_workspace.restype = ctypes.c_size_t
         L.seqm_sp2_workspace.argtypes = [ctypes.c_int64, ctypes.c_int64]
@@ -80,6 +78,7 @@ def lib():
         L.seqm_elec_energy_workspace.restype = ctypes.c_size_t
         L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
         L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
+        L.seqm_sp2_density_async.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, ci, VP, VP]
         L.seqm_nccl_unique_id.argtypes = [VP]
         L.seqm_nccl_comm_create.argtypes = [VP, ci, ci, ctypes.POINTER(VP)]
         L.seqm_nccl_comm_destroy.argtypes = [VP]
@@ -103,11 +102,9 @@ def lib():
         for name in EXPORTS:
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
-                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused', 'seqm_scf_warps',
+                            'seqm_launch_count', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused',
                             'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
                 fn.restype = ctypes.c_int
-        if os.environ.get('SEQM_SCF_WARPS'):
-            L.seqm_scf_warps(int(os.environ['SEQM_SCF_WARPS']))
         if os.environ.get('SEQM_EIGH_CFG'):
             L.seqm_eigh_block_config(int(os.environ['SEQM_EIGH_CFG']))
         if os.environ.get('SEQM_EIGH_TOL'):
@@ -118,7 +115,7 @@ def lib():
 
 EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile_enable', 'seqm_profile_report', 'seqm_atompar_bytes', 'seqm_atom_pack', 'seqm_hcore', 'seqm_w_expand',
            'seqm_fock', 'seqm_elec_energy', 'seqm_eigh_max_m', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_eigh_density', 'seqm_sp2_workspace',
-           'seqm_sp2_density', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf_warps', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
+           'seqm_sp2_density', 'seqm_sp2_density_async', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
            'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
            'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse']
 

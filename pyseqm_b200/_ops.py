@@ -2,6 +2,7 @@
 current CUDA stream, and wraps the pair pass + its hand-written adjoint as a torch.autograd.Function so
 `Force`'s `L.backward()` and `ForceXL`'s `grad(L, coordinates)` work as in the reference."""
 import ctypes
+import warnings
 
 import torch
 
@@ -134,6 +135,23 @@ def sp2_density(F, nheavy, nhydro, nocc, molsize, mmax, eps, active=None, want_n
     return (D, nit) if want_niter else D
 
 
+def sp2_density_async(F, nheavy, nhydro, nocc, molsize, mmax, eps, steps, work=None, D=None, unfinished=None):
+    """fixed number of purification steps, no host synchronisation (CUDA-graph capturable); unfinished (int32[1] on the
+    device) receives the number of molecules that would have needed more steps"""
+    F = _f64(F)
+    B = F.shape[0]
+    if D is None:
+        D = torch.zeros_like(F)
+    if work is None:
+        work = torch.empty(lib().seqm_sp2_workspace(B, molsize), dtype=torch.uint8, device=F.device)
+    if unfinished is None:
+        unfinished = torch.zeros(1, dtype=torch.int32, device=F.device)
+    check(lib().seqm_sp2_density_async(B, molsize, int(mmax), _p(F), _p(nheavy), _p(nhydro), _p(nocc), float(eps), _p(None),
+                                       _p(D), _p(None), _p(work), int(steps), _p(unfinished), _stream()),
+          'seqm_sp2_density_async')
+    return D, unfinished
+
+
 # ---- tile-sharded SP2 (single large system over the GPUs of one box; include/seqm_b200.h, sp2_kernels.cu) ----
 _sp2_shard = {'comm': None, 'ranks': 0}      # handle of seqm_nccl_comm_create / number of (emulated) ranks
 
@@ -199,6 +217,11 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv, status=N
     opt.debug = 1 if debug else 0
     if opt.converger not in (0, 1, 2):
         raise ValueError("scf_converger should be [0, alpha], [1] or [2]")
+    if opt.use_sp2 and not getattr(topo, 'uniform', True):
+        warnings.warn("sp2 on a batch of mixed molecule sizes: pyseqm_b200 purifies every molecule at its own packed size; "
+                      "the reference zero-pads all molecules to the largest one before SP2 (pack.py:28, SP2.py:30-41), so "
+                      "its Gershgorin bounds and traces include the padding and its density differs at the level of the "
+                      "SP2 tolerance (tests/test_gpu_golden_big.py::test_sp2_mixed_sizes)", stacklevel=3)
     use_async = status is not None and scf_is_fused(topo, sp2, debug)
     opt.async_status = 1 if use_async else 0
     P = _f64(P0).clone()

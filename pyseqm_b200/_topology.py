@@ -55,7 +55,9 @@ class PairTopology:
             self.nheavy = nHeavy.to(i32).contiguous()
             self.nhydro = nHydro.to(i32).contiguous()
             self.nocc = nocc.to(i32).contiguous()
-            self.mmax = int((4 * nHeavy + nHydro).max()) if self.nmol else 0
+            msz = 4 * nHeavy + nHydro
+            self.mmax = int(msz.max()) if self.nmol else 0
+            self.uniform = bool(self.nmol == 0 or int(msz.min()) == self.mmax)      # every molecule has the same packed size
         t = Topology()
         t.nmol, t.molsize, t.natoms, t.npairs = self.nmol, S, self.natoms, self.npairs
         t.Z, t.atom_mol, t.atom_slot = self.Z.data_ptr(), self.atom_mol.data_ptr(), self.atom_slot.data_ptr()

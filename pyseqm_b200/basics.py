@@ -215,8 +215,20 @@ class Force(torch.nn.Module):
         if self.create_graph:
             raise NotImplementedError("2nd_grad (second derivatives) is outside the B200 hot path")
         self.seqm_parameters = seqm_parameters
+        # pyseqm_b200 extension (not a reference key): report SCF non-convergence of call k (the warning and
+        # last_state['iterations']) when call k+1 starts instead of blocking the host at the end of call k, so the
+        # host can enqueue the next step while the GPU still runs this one.  `notconverged` is returned as usual.
+        self.defer_scf_warning = bool(seqm_parameters.get('defer_scf_warning', False))
+        self._pending = []
+
+    def flush_status(self):
+        """resolve the deferred SCF status of earlier calls (defer_scf_warning)"""
+        while self._pending:
+            _engine.resolve_status(self._pending.pop(0))
 
     def forward(self, const, coordinates, species, learned_parameters=dict(), P0=None, step=0, *args, **kwargs):
+        while self._pending and (len(self._pending) > 2 or _engine.resolve_status(self._pending[0], wait=False)):
+            _engine.resolve_status(self._pending.pop(0))
         coordinates.requires_grad_(True)
         self.energy._defer_status = True
         try:
@@ -229,7 +241,10 @@ class Force(torch.nn.Module):
         t0 = _engine._tic(const)
         L.backward()
         _engine._toc(const, "Force", t0)
-        _engine.resolve_status(self.energy.last_state)      # SCF status (non-convergence warning) without a mid-call sync
+        if self.defer_scf_warning and 'status' in self.energy.last_state:
+            self._pending.append(self.energy.last_state)
+        else:
+            _engine.resolve_status(self.energy.last_state)      # SCF status (non-convergence warning) without a mid-call sync
         force = -coordinates.grad.detach()
         coordinates.grad = torch.zeros_like(coordinates.grad)
         return force, P, Etot, Hf, Eelec, Enuc, Eiso, EnucAB, e, charge, notconverged

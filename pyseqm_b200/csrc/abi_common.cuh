@@ -1,6 +1,7 @@
 // Host-side helpers shared by the extern "C" entry points.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdio>
 #include <string>
 
@@ -12,8 +13,11 @@ namespace seqm {
 void set_error(const std::string& s);
 // launch accounting and the optional event profiler (seqm_profile_*): prof_mark(name) opens a region that
 // lasts until the next mark on the same stream
-extern unsigned long long g_launches;
+extern std::atomic<unsigned long long> g_launches;      // entry points may be called from several host threads
 void prof_mark(const char* name, cudaStream_t st);
+// 512 bytes of page-locked host memory owned by the calling thread (allocated on first use, kept for the life of the
+// thread's library use): the status word a host-driven loop reads back; nullptr if the allocation fails
+unsigned long long* host_status_slot();
 
 // SP2 sharding hook of the SCF driver (sp2_kernels.cu, seqm_scf_sp2_comm)
 extern void* g_scf_sp2_comm;

@@ -30,10 +30,6 @@ int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, con
                      const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out,
                      int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st);
 
-int launch_eigh_pair(int64_t nmol, int64_t molsize, int mp, const double* F, const int32_t* nheavy, const int32_t* nhydro,
-                     const int32_t* nocc, const uint8_t* active, double* P, int32_t* info, double* Vstore, int warm,
-                     double tol, cudaStream_t st);
-extern int g_scf_warps;
 
 double eigh_tolerance();
 size_t scf_small_scratch_bytes(int64_t nmol);

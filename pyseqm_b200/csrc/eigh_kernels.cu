@@ -226,8 +226,8 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
   }
 }
 
-double g_eigh_tol = 1.0e-18;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel; 1e-24 until r01q: one sweep more, same result to 1e-11 eV)
-double g_eigh_tol_warp = 1.0e-18; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
+double g_eigh_tol = 1.0e-16;      // off-diagonal^2 / total^2 at which one last sweep is run (CTA kernel; 1e-24 until r01q: one sweep more, same result to 1e-11 eV)
+double g_eigh_tol_warp = 1.0e-16; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
 double eigh_tolerance() { return g_eigh_tol_warp; }
 int g_eigh_cfg = 3;      // variant hook (seqm_eigh_block_config): bit 0: 256-thread CTAs + FP32 tangent for 32 < m <= 48, bit 1: FP32 tangent for m <= 64
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
@@ -269,9 +269,7 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
   const size_t smem = eigh_smem_bytes(mp, Vstore != nullptr);
   prof_mark("eigh_density", st);
   int rc;
-  if (mp <= 32 && !g_force_block_jacobi && g_scf_warps == 2 && !e_out && !v_out)
-    rc = launch_eigh_pair(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, info, Vstore, warm, g_eigh_tol_warp, st);
-  else if (mp <= 32 && !g_force_block_jacobi)
+  if (mp <= 32 && !g_force_block_jacobi)
     rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 32)
     rc = launch_cfg<256, 7, false>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
@@ -298,8 +296,8 @@ void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
 void seqm_eigh_block_config(int bits) { g_eigh_cfg = bits; }
 
 void seqm_eigh_tolerance(double tol) {
-  g_eigh_tol = tol > 0.0 ? tol : 1.0e-18;
-  g_eigh_tol_warp = tol > 0.0 ? tol : 1.0e-18;
+  g_eigh_tol = tol > 0.0 ? tol : 1.0e-16;
+  g_eigh_tol_warp = tol > 0.0 ? tol : 1.0e-16;
 }
 
 int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,

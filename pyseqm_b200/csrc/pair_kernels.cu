@@ -7,6 +7,7 @@
 //            two_elec_two_center_int_local_frame.py:18-281, diat_overlap.py:3-393, cal_par.py:8-173,
 //            energy.py:38-78; adjoint = what autograd replays for basics.py:369-388.
 #include <map>
+#include <mutex>
 #include <vector>
 
 #include "abi_common.cuh"
@@ -17,8 +18,9 @@ namespace seqm {
 thread_local std::string g_last_error;
 void set_error(const std::string& s) { g_last_error = s; }
 
-unsigned long long g_launches = 0;
-static bool g_prof_on = false;
+std::atomic<unsigned long long> g_launches{0};
+static std::atomic<bool> g_prof_on{false};
+static std::mutex g_prof_mutex;      // g_marks is appended to from every calling thread
 struct ProfMark { std::string name; cudaEvent_t ev; };
 static std::vector<ProfMark> g_marks;
 void prof_mark(const char* name, cudaStream_t st) {
@@ -27,7 +29,18 @@ void prof_mark(const char* name, cudaStream_t st) {
   m.name = name;
   cudaEventCreate(&m.ev);
   cudaEventRecord(m.ev, st);
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
   g_marks.push_back(m);
+}
+
+unsigned long long* host_status_slot() {
+  struct Slot {
+    unsigned long long* p = nullptr;
+    ~Slot() { if (p) cudaFreeHost(p); }
+  };
+  static thread_local Slot slot;
+  if (!slot.p && cudaMallocHost(&slot.p, 512) != cudaSuccess) { cudaGetLastError(); slot.p = nullptr; }
+  return slot.p;
 }
 
 __constant__ double c_tore[19] = {0, 1, 0, 1, 2, 3, 4, 5, 6, 7, 0, 1, 2, 3, 4, 5, 6, 7, 0};
@@ -586,9 +599,10 @@ extern "C" {
 
 const char* seqm_last_error(void) { return g_last_error.c_str(); }
 
-unsigned long long seqm_launch_count(void) { return g_launches; }
+unsigned long long seqm_launch_count(void) { return g_launches.load(); }
 
 void seqm_profile_enable(int on) {
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
   for (auto& m : g_marks) cudaEventDestroy(m.ev);
   g_marks.clear();
   g_prof_on = on != 0;
@@ -597,6 +611,7 @@ void seqm_profile_enable(int on) {
 // "name total_ms count\n" per region name; synchronises the device
 int seqm_profile_report(char* buf, size_t cap) {
   cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
   std::map<std::string, std::pair<double, int>> acc;
   for (size_t i = 0; i + 1 < g_marks.size(); ++i) {
     if (g_marks[i].name == "end") continue;

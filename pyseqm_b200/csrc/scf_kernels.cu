@@ -362,8 +362,8 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, wk.red, st);
   if (rc) return rc;
 
-  unsigned long long* hstat = nullptr;
-  SEQM_CUDA(cudaMallocHost(&hstat, 64));
+  unsigned long long* hstat = host_status_slot();
+  SEQM_REQUIRE(hstat, "seqm_scf: no page-locked status slot");
   int k = 0;
   long long left = B;
   const int max_iter = opt->max_iter > 0 ? opt->max_iter : 1000;
@@ -450,7 +450,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     SEQM_CHECK_LAUNCH("mix_kernel");
     return SEQM_OK;
   };
-#define SEQM_TRY(x) do { rc = (x); if (rc) { cudaFreeHost(hstat); return rc; } } while (0)
+#define SEQM_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
 
   int counter = -1, cF = 0;
   if (opt->converger == 0) {
@@ -494,7 +494,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
         pulay_coeff_kernel<<<cdiv(B, 128), 128, 0, st>>>(B, counter, cF, nc, wk.EMAT, wk.coeff);
         pulay_extrapolate_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, cF, nc, wk.coeff, wk.FOCK, F);
         g_launches += 2;
-        { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); cudaFreeHost(hstat); return SEQM_ECUDA; } }
+        { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); return SEQM_ECUDA; } }
         SEQM_TRY(density(P));
         SEQM_TRY(refock_and_finish(true, counter, cF));
         if (k >= max_iter) break;
@@ -502,7 +502,6 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     }
   }
   prof_mark("end", st);
-  cudaFreeHost(hstat);
   if (iterations_out) { iterations_out[0] = k; iterations_out[1] = (int32_t)left; }
   return SEQM_OK;
 }

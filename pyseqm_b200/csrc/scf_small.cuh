@@ -1,4 +1,4 @@
-// shared by scf_small_kernels.cu (one warp per molecule) and scf_small2_kernels.cu (two warps per molecule)
+// device code of scf_small_kernels.cu (one warp per molecule)
 #pragma once
 #include "eigh_warp.cuh"
 

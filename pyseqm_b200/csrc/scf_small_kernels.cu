@@ -405,8 +405,6 @@ static int launch_small_n(int64_t nmol, const SmallScfArgs& args, cudaStream_t s
   return SEQM_OK;
 }
 
-int g_scf_warps = 1;      // warps per molecule in the one-launch SCF and the small Jacobi (seqm_scf_warps)
-int launch_scf_small2(int64_t nmol, int mp, const SmallScfArgs& a, cudaStream_t st);
 
 size_t scf_small_scratch_bytes(int64_t nmol) { return (size_t)(nmol + 1) * sizeof(int32_t); }
 
@@ -427,11 +425,6 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
   a.FPPF = FPPF; a.EMAT = EMAT; a.Vstore = Vstore; a.stat = stat; a.nn = nn; a.converger = converger;
   a.max_iter = max_iter; a.alpha = alpha; a.eps = eps; a.tol = tol;
   int rc;
-  if (g_scf_warps == 2) {
-    rc = launch_scf_small2(t.nmol, mp, a, st);
-    prof_mark("end", st);
-    return rc;
-  }
 #define SEQM_SMALL_CASE(NN) if (mp <= NN) { rc = launch_small_n<NN>(t.nmol, a, st); prof_mark("end", st); return rc; }
   SEQM_SMALL_CASE(8)
   SEQM_SMALL_CASE(12)
@@ -446,7 +439,6 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
 }
 
 }  // namespace seqm
-extern "C" void seqm_scf_warps(int n) { seqm::g_scf_warps = n == 2 ? 2 : 1; }
 namespace seqm {
 #ifdef SEQM_SCF_TIMING
 }  // namespace seqm

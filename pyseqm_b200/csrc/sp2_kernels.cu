@@ -600,6 +600,10 @@ static bool sp2_p2p_ready(SeqmComm* cm, size_t doubles) {
     cudaDeviceSynchronize();
     for (int q = 0; q < n; ++q)
       if (q != cm->rank && cm->rec_peer[q]) cudaIpcCloseMemHandle(cm->rec_peer[q]);
+    if (cm->bar) {      // no rank frees its buffer before every peer has unmapped it
+      double* cb = cm->bar + (size_t)13 * n;
+      if (api->AllGather(cb + cm->rank, cb, 1, NCCL_FLOAT64, cm->comm, cm->side) == 0) cudaStreamSynchronize(cm->side);
+    }
     cudaFree(cm->rec_own);
     cm->rec_own = nullptr;
   }
@@ -648,9 +652,17 @@ static bool sp2_p2p_ready(SeqmComm* cm, size_t doubles) {
 }
 
 // shared implementation; nranks == 0: the single-GPU form (tiles written straight into X)
+// async_steps > 0: exactly that many (rounded up to even) purification steps are enqueued and nothing is read back -
+// no host synchronisation, no host allocation, capturable in a CUDA graph; d_unfinished (device) receives the number of
+// molecules still live after the last step.  async_steps == 0: the host reads the per-step live counters back; the
+// first read comes after as many steps as the previous call needed (g_sp2_hint), so a steady-state call (MD, SCF)
+// synchronises once.
+static std::atomic<int> g_sp2_hint{2};
+constexpr int SP2_NCOUNT = 64;      // per-step live counters kept on the device (256 bytes of the workspace)
 static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int mmax, const double* F,
                    const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
-                   const uint8_t* active, double* D, int32_t* niter, void* work, void* stream) {
+                   const uint8_t* active, double* D, int32_t* niter, void* work, void* stream,
+                   int async_steps = 0, int32_t* d_unfinished = nullptr) {
   SEQM_REQUIRE(F && nheavy && nhydro && nocc && D && work && nmol >= 0 && molsize > 0, "seqm_sp2_density: bad argument");
   if (nmol == 0) return SEQM_OK;
   SEQM_REQUIRE(mmax >= 1 && mmax <= 4 * molsize, "seqm_sp2_density: mmax");
@@ -670,7 +682,7 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   Sp2Step* state = (Sp2Step*)base; base += al256(2 * nmol * sizeof(Sp2Step));
   double* partial = (double*)base; base += al256((size_t)2 * nmol * 2 * sp2_tiles((int)ldmax) * 8);
   double* occ = (double*)base; base += al256(nmol * 8);
-  int* nlive = (int*)base; base += 256;      // [2]
+  int* nlive = (int*)base; base += 256;      // [SP2_NCOUNT] per-step live counters
   double* part0 = (double*)base; base += al256((size_t)nmol * red_chunks(ldmax * ldmax) * 16);
   double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
   const long long stride = (long long)ld * ld;
@@ -691,8 +703,8 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   SEQM_CHECK_LAUNCH("sp2_x0_kernel");
   sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, xchunks, dims, nocc, active, part0, state, partial, occ);
   SEQM_CHECK_LAUNCH("sp2_step_init_kernel");
-  int* hlive = nullptr;
-  SEQM_CUDA(cudaMallocHost(&hlive, 2 * sizeof(int)));
+  int* hlive = async_steps > 0 ? nullptr : (int*)host_status_slot();
+  SEQM_REQUIRE(async_steps > 0 || hlive, "seqm_sp2_density: no page-locked status slot");
   int rc = SEQM_OK;
   auto check = [&](const char* what) {
     cudaError_t e_ = cudaGetLastError();
@@ -764,30 +776,50 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
     // this call's first launch is about to store into (cm->bar: [0, 2n) step barriers, [12n, 13n) this one)
     double* eb = cm->bar + (size_t)12 * nranks;
     const int r = api->AllGather(eb + myrank, eb, 1, NCCL_FLOAT64, cm->comm, st);
-    if (r) { set_error(std::string("ncclAllGather (entry barrier): ") + api->GetErrorString(r)); cudaFreeHost(hlive); return SEQM_ECUDA; }
+    if (r) { set_error(std::string("ncclAllGather (entry barrier): ") + api->GetErrorString(r)); return SEQM_ECUDA; }
   }
-  // two purification steps per host synchronisation: the second is a no-op (CTAs exit on the live flag) when the
-  // first one finished every molecule
-  for (int it = 0; it < 200 && rc == SEQM_OK; it += 2) {
-    prof_mark("sp2_step", st);
-    cudaMemsetAsync(nlive, 0, 2 * sizeof(int), st);
-    for (int h = 0; h < 2 && rc == SEQM_OK; ++h) {
-      if (p2p) { p2p_step(it + h, nlive + h); continue; }
-      if (sharded) { sharded_step(it + h, nlive + h); continue; }
-      for (int b0 = 0; b0 < B && rc == SEQM_OK; b0 += 65535) {
-        const int nb = B - b0 < 65535 ? B - b0 : 65535;
-        sp2_step_kernel<false><<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it + h, eps, dims, occ, X0, X1, stride,
-                                                               state, partial, nlive + h, 0, 1, Sp2Peers{}, 0);
-        check("sp2_step_kernel");
-      }
+  // Steps are enqueued in batches; step `it` counts the molecules it leaves live in nlive[it % SP2_NCOUNT] and is a
+  // no-op for finished molecules (their CTAs exit on the live flag), so running past convergence is harmless.
+  auto enqueue = [&](int it) {
+    int* counter = nlive + (it % SP2_NCOUNT);
+    if (p2p) { p2p_step(it, counter); return; }
+    if (sharded) { sharded_step(it, counter); return; }
+    for (int b0 = 0; b0 < B && rc == SEQM_OK; b0 += 65535) {
+      const int nb = B - b0 < 65535 ? B - b0 : 65535;
+      sp2_step_kernel<false><<<dim3(ntile, nb), 256, 0, st>>>(B, b0, ld, T, it, eps, dims, occ, X0, X1, stride, state,
+                                                             partial, counter, 0, 1, Sp2Peers{}, 0);
+      check("sp2_step_kernel");
     }
-    if (rc) break;
-    cudaMemcpyAsync(hlive, nlive, 2 * sizeof(int), cudaMemcpyDeviceToHost, st);
-    cudaError_t e = cudaStreamSynchronize(st);
-    if (e != cudaSuccess) { set_error(std::string("sp2 loop: ") + cudaGetErrorString(e)); rc = SEQM_ECUDA; break; }
-    if (hlive[0] == 0 || hlive[1] == 0) break;
+  };
+  if (async_steps > 0) {
+    const int nst = (async_steps + 1) & ~1;
+    SEQM_REQUIRE(nst <= SP2_NCOUNT, "seqm_sp2_density_async: at most 64 steps");
+    prof_mark("sp2_step", st);
+    cudaMemsetAsync(nlive, 0, SP2_NCOUNT * sizeof(int), st);
+    for (int it = 0; it < nst && rc == SEQM_OK; ++it) enqueue(it);
+    if (rc) return rc;
+    if (d_unfinished) SEQM_CUDA(cudaMemcpyAsync(d_unfinished, nlive + (nst - 1), sizeof(int), cudaMemcpyDeviceToDevice, st));
+  } else {
+    int done = 0;
+    int batch = g_sp2_hint.load();
+    if (batch < 2) batch = 2;
+    if (batch > SP2_NCOUNT) batch = SP2_NCOUNT;
+    batch = (batch + 1) & ~1;
+    for (int it = 0; it < 200 && rc == SEQM_OK && !done;) {
+      prof_mark("sp2_step", st);
+      cudaMemsetAsync(nlive, 0, SP2_NCOUNT * sizeof(int), st);
+      const int it0 = it;
+      for (int h = 0; h < batch && rc == SEQM_OK; ++h, ++it) enqueue(it);
+      if (rc) break;
+      cudaMemcpyAsync(hlive, nlive, SP2_NCOUNT * sizeof(int), cudaMemcpyDeviceToHost, st);
+      cudaError_t e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess) { set_error(std::string("sp2 loop: ") + cudaGetErrorString(e)); rc = SEQM_ECUDA; break; }
+      for (int q = it0; q < it; ++q)
+        if (hlive[q % SP2_NCOUNT] == 0) { done = q + 1; break; }
+      batch = 2;
+    }
+    if (done) g_sp2_hint.store((done + 1) & ~1);
   }
-  cudaFreeHost(hlive);
   if (rc) return rc;
   int fchunks = (int)(((long long)mmax * mmax + 255) / 256);
   if (fchunks > 512) fchunks = 512;
@@ -806,6 +838,14 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
                      int32_t* niter, void* work, void* stream) {
   return sp2_run(nullptr, 0, nmol, molsize, mmax, F, nheavy, nhydro, nocc, eps, active, D, niter, work, stream);
+}
+
+int seqm_sp2_density_async(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                           const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
+                           int32_t* niter, void* work, int steps, int32_t* unfinished, void* stream) {
+  SEQM_REQUIRE(steps > 0, "seqm_sp2_density_async: steps");
+  return sp2_run(nullptr, 0, nmol, molsize, mmax, F, nheavy, nhydro, nocc, eps, active, D, niter, work, stream, steps,
+                 unfinished);
 }
 
 int seqm_sp2_density_nccl(void* comm, int emulate_ranks, int64_t nmol, int64_t molsize, int mmax, const double* F,

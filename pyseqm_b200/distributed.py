@@ -25,21 +25,47 @@ def shard_batch(species, coordinates, rank=None, world=None):
     return species[lo:hi], coordinates[lo:hi], (lo, hi)
 
 
-def gather_molecules(local, nmol, world=None):
-    """per-molecule results of every rank -> the global batch order, on every rank.  Shards may differ in length
-    by one molecule: the short ones are padded for the all_gather and trimmed afterwards."""
-    world = dist.get_world_size() if world is None else world
+_GATHER_BUF = {}      # (shape of the padded shard, dtype, device, world) -> (send buffer, receive buffer)
+
+
+class GatheredMolecules:
+    """handle of an asynchronous gather_molecules(): .wait() -> the global-order tensor"""
+
+    def __init__(self, work, recv, bounds, longest):
+        self._work, self._recv, self._bounds, self._longest = work, recv, bounds, longest
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+        if all(hi - lo == self._longest for lo, hi in self._bounds):
+            return self._recv.reshape((-1,) + tuple(self._recv.shape[2:]))
+        return torch.cat([self._recv[r, :hi - lo] for r, (lo, hi) in enumerate(self._bounds)], dim=0)
+
+
+def gather_molecules(local, nmol, world=None, async_op=False, group=None):
+    """per-molecule results of every rank -> the global batch order, on every rank.  ONE all_gather_into_tensor into a
+    receive buffer that is allocated once per shard shape (shards may differ in length by one molecule: the short ones
+    are padded in the send buffer and trimmed on the way out).  async_op=True returns a GatheredMolecules handle at
+    once - the collective runs on NCCL's stream while the caller enqueues the next step - and .wait() orders the
+    current stream behind it when the result is consumed."""
+    world = dist.get_world_size(group) if world is None else world
     bounds = shard_bounds(nmol, world)
     longest = max(hi - lo for lo, hi in bounds)
-    pad = longest - local.shape[0]
-    if pad < 0:
+    if local.shape[0] > longest:
         raise ValueError("local shard is longer than shard_bounds allows")
-    buf = local.detach().contiguous()
-    if pad:
-        buf = torch.cat([buf, buf.new_zeros((pad,) + tuple(buf.shape[1:]))], dim=0)
-    parts = [torch.empty_like(buf) for _ in range(world)]
-    dist.all_gather(parts, buf)
-    return torch.cat([p[:hi - lo] for p, (lo, hi) in zip(parts, bounds)], dim=0)
+    tail = tuple(local.shape[1:])
+    key = ((longest,) + tail, local.dtype, str(local.device), world)
+    bufs = _GATHER_BUF.get(key)
+    if bufs is None:
+        bufs = (torch.zeros((longest,) + tail, dtype=local.dtype, device=local.device),
+                torch.empty((world, longest) + tail, dtype=local.dtype, device=local.device))
+        _GATHER_BUF[key] = bufs
+    send, recv = bufs
+    send[:local.shape[0]].copy_(local.detach())
+    work = dist.all_gather_into_tensor(recv.reshape((world * longest,) + tail), send, group=group, async_op=True)
+    handle = GatheredMolecules(work, recv, bounds, longest)
+    return handle if async_op else handle.wait()
 
 
 # ---- single large system (BASELINE.json configs[4]): SP2 tiles sharded over the ranks -------------------------

@@ -108,12 +108,12 @@ def _rot_to(v, target):
     return np.eye(3) + K + K @ K / (1.0 + c)
 
 
-def _grow_molecule(rng, natoms):
+def _grow_molecule(rng, natoms, attempts=50):
     """A saturated acyclic C/N/O skeleton with tetrahedral local geometry, every free valence
     capped by H: closed shell by construction and well-behaved in SCF.  Returns (Z, xyz) sorted by
     descending Z, with about `natoms` atoms."""
     nheavy = max(1, int(round((natoms - 2) / 3.0)))
-    for _attempt in range(50):
+    for _attempt in range(attempts):
         elems = rng.choice([6, 7, 8], size=nheavy, p=[0.75, 0.125, 0.125])
         elems[0] = 6
         pos = [np.zeros(3)]
@@ -164,7 +164,7 @@ def _grow_molecule(rng, natoms):
     raise RuntimeError("could not grow a molecule")
 
 
-def mixed_organics(nmol, seed=0, min_atoms=5, max_atoms=30):
+def mixed_organics(nmol, seed=0, min_atoms=5, max_atoms=30, attempts=50):
     """Random saturated C/N/O/H molecules of about min_atoms..max_atoms atoms, padded to max_atoms."""
     rng = np.random.RandomState(seed)
     S = max_atoms
@@ -172,9 +172,9 @@ def mixed_organics(nmol, seed=0, min_atoms=5, max_atoms=30):
     coords = np.zeros((nmol, S, 3), dtype=np.float64)
     for b in range(nmol):
         n = int(rng.randint(min_atoms, max_atoms + 1))
-        Z, xyz = _grow_molecule(rng, n)
+        Z, xyz = _grow_molecule(rng, n, attempts)
         while len(Z) > S:
-            Z, xyz = _grow_molecule(rng, n - 1)
+            Z, xyz = _grow_molecule(rng, n - 1, attempts)
         species[b, :len(Z)] = Z
         coords[b, :len(Z)] = xyz
     return _finish(species, coords)

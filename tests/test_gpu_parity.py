@@ -195,12 +195,11 @@ def _mixed_sizes(g):
     return len(set((4 * g['nHeavy'] + g['nHydro']).tolist())) > 1
 
 
-@pytest.mark.parametrize('path', ['fused', 'fused_2warp', 'host_loop'])
+@pytest.mark.parametrize('path', ['fused', 'host_loop'])
 @pytest.mark.parametrize('name', golden_names())
 def test_force_end_to_end(name, path):
     """Force (Parser -> pair pass -> SCF -> adjoint) against the reference's outputs.  'fused': the one-launch SCF
     kernel for batches with packed size <= 32 (falls through to the host loop for the larger ones);
-    'fused_2warp': the same with two warps per molecule (experiment hook seqm_scf_warps);
     'host_loop': the iteration-by-iteration driver, with the reference's debug print"""
     from pyseqm_b200 import _lib
     from pyseqm_b200.basics import Force
@@ -217,14 +216,12 @@ def test_force_end_to_end(name, path):
     species, coords = _t(g['species'], dev), _t(g['coords'], dev)
     scf_loop.debug = path == 'host_loop'
     _lib.lib().seqm_scf_fused(0 if path == 'host_loop' else 1)
-    _lib.lib().seqm_scf_warps(2 if path == 'fused_2warp' else 1)
     try:
         fmod = Force(sp).to(dev)
         force, P, Etot, Hf, Eelec, Enuc, Eiso, EnucAB, e, charge, notconv = fmod(const, coords, species)
     finally:
         scf_loop.debug = False
         _lib.lib().seqm_scf_fused(1)
-        _lib.lib().seqm_scf_warps(1)
     st = fmod.energy.last_state
     assert abs(int(st['iterations']) - len(g['trace'])) <= 1          # SCF iteration count of the reference +-1
     assert int(st['niter'].max()) == int(st['iterations'])
