@@ -2,7 +2,6 @@
 current CUDA stream, and wraps the pair pass + its hand-written adjoint as a torch.autograd.Function so
 `Force`'s `L.backward()` and `ForceXL`'s `grad(L, coordinates)` work as in the reference."""
 import ctypes
-import warnings
 
 import torch
 
@@ -217,11 +216,6 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv, status=N
     opt.debug = 1 if debug else 0
     if opt.converger not in (0, 1, 2):
         raise ValueError("scf_converger should be [0, alpha], [1] or [2]")
-    if opt.use_sp2 and not getattr(topo, 'uniform', True):
-        warnings.warn("sp2 on a batch of mixed molecule sizes: pyseqm_b200 purifies every molecule at its own packed size; "
-                      "the reference zero-pads all molecules to the largest one before SP2 (pack.py:28, SP2.py:30-41), so "
-                      "its Gershgorin bounds and traces include the padding and its density differs at the level of the "
-                      "SP2 tolerance (tests/test_gpu_golden_big.py::test_sp2_mixed_sizes)", stacklevel=3)
     use_async = status is not None and scf_is_fused(topo, sp2, debug)
     opt.async_status = 1 if use_async else 0
     P = _f64(P0).clone()

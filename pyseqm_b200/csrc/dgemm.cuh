@@ -31,6 +31,11 @@ int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, con
                      int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st);
 
 
+int eigh_cluster_max_m();
+int launch_eigh_cluster(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
+                        const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
+                        double* v_out, int32_t* info, double tol, cudaStream_t st);
+
 double eigh_tolerance();
 size_t scf_small_scratch_bytes(int64_t nmol);
 int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, const double* g_ss, const double* g_pp,

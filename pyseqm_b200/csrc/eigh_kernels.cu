@@ -8,6 +8,8 @@
 // diag.py:140-144.  The warm start does not change the result (the decomposition is still converged to
 // 1e-14 of the norm); it cuts the sweeps from ~9 to 2-3 because consecutive Fock matrices are close.
 // reference: seqm/seqm_functions/diag.py:102-172
+#include <mutex>
+
 #include "abi_common.cuh"
 #include "dgemm.cuh"
 
@@ -245,10 +247,16 @@ template <int NT, int MINB, bool FAST_T>
 static int launch_cfg(int64_t nmol, size_t smem, cudaStream_t st, int S, int mp, const double* F, const int32_t* nheavy,
                       const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
                       double* v_out, int32_t* info, double* Vstore, int warm, double tol) {
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB, FAST_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+  // the attribute belongs to the function, not to the calling thread: it only ever grows (a worker thread of
+  // BucketedBatch with a smaller bucket must not lower the limit another thread is about to launch with)
+  static std::mutex mtx;
+  static size_t configured = 0;
+  if (smem > 48 * 1024) {
+    std::lock_guard<std::mutex> lock(mtx);
+    if (smem > configured) {
+      SEQM_CUDA(cudaFuncSetAttribute(eigh_density_kernel<NT, MINB, FAST_T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
   }
   eigh_density_kernel<NT, MINB, FAST_T><<<(unsigned)nmol, NT, smem, st>>>(S, mp, F, nheavy, nhydro, nocc, active, P, e_out,
                                                                   v_out, info, Vstore, warm, tol);
@@ -262,7 +270,12 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
                         const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,
                         double* e_out, double* v_out, int32_t* info, double* Vstore, int warm, cudaStream_t st) {
   if (nmol == 0) return SEQM_OK;
-  if (mmax > EIGH_MAX_M) return fail(SEQM_EUNSUPPORTED, "seqm_eigh_density: packed size above the shared-memory Jacobi limit (118); use the SP2 density path");
+  if (mmax > EIGH_MAX_M) {      // beyond one CTA's shared memory: 8-CTA cluster, one-sided block Jacobi (eigh_cluster_kernels.cu)
+    prof_mark("eigh_cluster", st);
+    const int rc_ = launch_eigh_cluster(nmol, molsize, mmax, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, g_eigh_tol_warp, st);
+    prof_mark("end", st);
+    return rc_;
+  }
   if (mmax < 1) mmax = 1;
   if (mmax > EIGH_WARM_MAX_M) { Vstore = nullptr; warm = 0; }
   const int mp = (mmax + 1) & ~1;
@@ -291,7 +304,7 @@ using namespace seqm;
 
 extern "C" {
 
-int seqm_eigh_max_m(void) { return EIGH_MAX_M; }
+int seqm_eigh_max_m(void) { return eigh_cluster_max_m(); }
 void seqm_eigh_force_block(int on) { g_force_block_jacobi = on; }
 void seqm_eigh_block_config(int bits) { g_eigh_cfg = bits; }
 

@@ -82,10 +82,22 @@ __device__ __forceinline__ double blk_reduce(double v, double* red, int op) {   
 //   sp2_step_init_kernel  CTA per molecule: sums the partials in a fixed order, initial state of the fused loop
 constexpr int SP2_ROWS = 8;
 
+// The reference purifies pack(F[notconverged]) (scf_loop.py + pack.py:28): every molecule of the call zero padded to the
+// LARGEST ACTIVE molecule, and SP2.py:30-41 takes its Gershgorin bounds and traces over the padded matrix.  A zero row is
+// an orbital of energy 0 that never couples: all npad = padm - m of them carry the same scalar xp = hN/(hN - h1), which
+// follows the branch decisions (xp^2 or 2 xp - xp^2) and enters tr X and tr X^2 with weight npad.  Tracking that scalar
+// reproduces the reference's bounds, branches and stopping step exactly without touching the matrices.
+__global__ void sp2_padmax_kernel(int nmol, const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro,
+                                  const uint8_t* __restrict__ active, int* __restrict__ padm) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nmol || (active && !active[b])) return;
+  atomicMax(padm, 4 * nheavy[b] + nhydro[b]);
+}
+
 __global__ void __launch_bounds__(256)
 sp2_bounds_kernel(int S, int rchunks, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                   const int32_t* __restrict__ nhydro, const uint8_t* __restrict__ active, double* __restrict__ bounds,
-                  int32_t* __restrict__ dims) {
+                  int32_t* __restrict__ dims, const int* __restrict__ padm) {
   const int mol = blockIdx.x / rchunks, chunk = blockIdx.x - mol * rchunks;
   const int nh4 = 4 * nheavy[mol];
   const int m = nh4 + nhydro[mol];
@@ -116,6 +128,7 @@ sp2_bounds_kernel(int S, int rchunks, const double* __restrict__ F, const int32_
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int q = 1; q < SP2_ROWS; ++q) { lo = fmin(lo, slo[q]); hi = fmax(hi, shi[q]); }
+    if (chunk == 0 && m < *padm) { lo = fmin(lo, 0.0); hi = fmax(hi, 0.0); }      // the zero rows of the reference's padding
     bounds[((size_t)mol * rchunks + chunk) * 2] = lo;
     bounds[((size_t)mol * rchunks + chunk) * 2 + 1] = hi;
   }
@@ -124,7 +137,7 @@ sp2_bounds_kernel(int S, int rchunks, const double* __restrict__ F, const int32_
 __global__ void __launch_bounds__(256)
 sp2_x0_kernel(int S, int ld, int rchunks, int chunks, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
               const int32_t* __restrict__ nhydro, const uint8_t* __restrict__ active, const double* __restrict__ bounds,
-              double* __restrict__ X, double* __restrict__ part) {
+              double* __restrict__ X, double* __restrict__ part, const int* __restrict__ padm, double* __restrict__ padx) {
   const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
   const int nh4 = 4 * nheavy[mol];
   const int m = nh4 + nhydro[mol];
@@ -159,6 +172,13 @@ sp2_x0_kernel(int S, int ld, int rchunks, int chunks, const double* __restrict__
   tr = blk_reduce(tr, red, 0);
   fr = blk_reduce(fr, red, 0);
   if (threadIdx.x == 0) {
+    if (chunk == 0) {
+      const int npad = *padm > m ? *padm - m : 0;
+      const double xp = hN / sc;
+      padx[mol] = xp;
+      tr += npad * xp;
+      fr += npad * xp * xp;
+    }
     part[((size_t)mol * chunks + chunk) * 2] = tr;
     part[((size_t)mol * chunks + chunk) * 2 + 1] = fr;
   }
@@ -179,7 +199,8 @@ constexpr int SLDA = SBK + 4, SLDB = SBM + 4, SLDT = SBM + 1;
 
 struct Sp2Step {       // per molecule and parity
   double e0, e1;       // |tr X - nocc| after the last two steps
-  int live, niter, buf, pad;
+  double xp;           // value of the decoupled padding orbitals (reference zero padding, see sp2_padmax_kernel)
+  int live, niter, buf, pad;      // pad = number of padding orbitals
 };
 
 __device__ __forceinline__ void s_cp_async16(void* smem, const void* gmem, bool pred) {
@@ -230,6 +251,7 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
   double* pout = partial + ((size_t)((step + 1) & 1) * nmol + b) * 2 * ntile;
   double t1 = 0.0, t2 = 0.0;
   for (int q = 0; q < ntile; ++q) { t1 += pin[2 * q]; t2 += pin[2 * q + 1]; }
+  if (step > 0) { t1 += sin.pad * sin.xp; t2 += sin.pad * sin.xp * sin.xp; }      // step 0: already in the initial sums
   const double oc = occ[b];
   const bool square = fabs(t2 - oc) < fabs(2.0 * t1 - t2 - oc);
   const double tn = square ? t2 : 2.0 * t1 - t2;
@@ -241,7 +263,8 @@ sp2_step_kernel(int nmol, int b0, int ld, int T, int step, double eps, const int
     so.niter = sin.niter + 1;
     so.buf = (sin.buf ^ 1);
     so.live = ((so.e0 < eps) && (so.e1 < eps)) ? 0 : 1;
-    so.pad = 0;
+    so.pad = sin.pad;
+    so.xp = square ? sin.xp * sin.xp : 2.0 * sin.xp - sin.xp * sin.xp;
     state[(size_t)((step + 1) & 1) * nmol + b] = so;
     if (so.live) atomicAdd(nlive, 1);
   }
@@ -422,7 +445,7 @@ __global__ void __launch_bounds__(256)
 sp2_step_init_kernel(int nmol, int ntile, int chunks, const int32_t* __restrict__ dims,
                      const int32_t* __restrict__ nocc, const uint8_t* __restrict__ active,
                      const double* __restrict__ part, Sp2Step* __restrict__ state, double* __restrict__ partial,
-                     double* __restrict__ occ) {
+                     double* __restrict__ occ, const int* __restrict__ padm, const double* __restrict__ padx) {
   const int b = blockIdx.x;
   __shared__ double red[8];
   const bool live = (!active || active[b]) && dims[b] > 0;
@@ -440,7 +463,9 @@ sp2_step_init_kernel(int nmol, int ntile, int chunks, const int32_t* __restrict_
   if (threadIdx.x == 0) {
     const double oc = (double)nocc[b];
     Sp2Step s;
-    s.e0 = fabs(tr - oc); s.e1 = s.e0; s.live = live ? 1 : 0; s.niter = 0; s.buf = 0; s.pad = 0;
+    s.e0 = fabs(tr - oc); s.e1 = s.e0; s.live = live ? 1 : 0; s.niter = 0; s.buf = 0;
+    s.pad = (live && *padm > dims[b]) ? *padm - dims[b] : 0;
+    s.xp = s.pad ? padx[b] : 0.0;
     state[b] = s;
     s.live = 0;
     state[(size_t)nmol + b] = s;
@@ -512,7 +537,7 @@ static size_t sp2_core_bytes(int64_t nmol, int64_t molsize) {
   const size_t ld = (size_t)4 * molsize;       // upper bound of the packed size
   const size_t ntile = (size_t)sp2_tiles((int)ld);
   return 2 * al256((size_t)nmol * ld * ld * 8) + al256((size_t)nmol * sp2_rchunks((int)ld) * 16) + al256(nmol * 4) +
-         al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + al256(nmol * 8) + 256 +
+         al256(2 * nmol * sizeof(Sp2Step)) + al256(2 * nmol * 2 * ntile * 8) + 2 * al256(nmol * 8) + 256 + 256 +
          al256((size_t)nmol * red_chunks(ld * ld) * 16);
 }
 static size_t sp2_record_bytes(int64_t nmol, int64_t molsize, int nranks) {
@@ -682,6 +707,8 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   Sp2Step* state = (Sp2Step*)base; base += al256(2 * nmol * sizeof(Sp2Step));
   double* partial = (double*)base; base += al256((size_t)2 * nmol * 2 * sp2_tiles((int)ldmax) * 8);
   double* occ = (double*)base; base += al256(nmol * 8);
+  double* padx = (double*)base; base += al256(nmol * 8);
+  int* padm = (int*)base; base += 256;
   int* nlive = (int*)base; base += 256;      // [SP2_NCOUNT] per-step live counters
   double* part0 = (double*)base; base += al256((size_t)nmol * red_chunks(ldmax * ldmax) * 16);
   double* records = (double*)base;           // sharded form only: [sub][rank][molecule][tps] records
@@ -697,11 +724,14 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   prof_mark("sp2_init", st);
   const int rchunks = sp2_rchunks(ld), xchunks = red_chunks((size_t)ld * ld);
   SEQM_REQUIRE((long long)B * rchunks < (1LL << 31) && (long long)B * xchunks < (1LL << 31), "seqm_sp2_density: batch too large");
-  sp2_bounds_kernel<<<(unsigned)((size_t)B * rchunks), 256, 0, st>>>(S, rchunks, F, nheavy, nhydro, active, bounds, dims);
+  SEQM_CUDA(cudaMemsetAsync(padm, 0, sizeof(int), st));
+  sp2_padmax_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, nheavy, nhydro, active, padm);
+  SEQM_CHECK_LAUNCH("sp2_padmax_kernel");
+  sp2_bounds_kernel<<<(unsigned)((size_t)B * rchunks), 256, 0, st>>>(S, rchunks, F, nheavy, nhydro, active, bounds, dims, padm);
   SEQM_CHECK_LAUNCH("sp2_bounds_kernel");
-  sp2_x0_kernel<<<(unsigned)((size_t)B * xchunks), 256, 0, st>>>(S, ld, rchunks, xchunks, F, nheavy, nhydro, active, bounds, X0, part0);
+  sp2_x0_kernel<<<(unsigned)((size_t)B * xchunks), 256, 0, st>>>(S, ld, rchunks, xchunks, F, nheavy, nhydro, active, bounds, X0, part0, padm, padx);
   SEQM_CHECK_LAUNCH("sp2_x0_kernel");
-  sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, xchunks, dims, nocc, active, part0, state, partial, occ);
+  sp2_step_init_kernel<<<B, 256, 0, st>>>(B, ntile, xchunks, dims, nocc, active, part0, state, partial, occ, padm, padx);
   SEQM_CHECK_LAUNCH("sp2_step_init_kernel");
   int* hlive = async_steps > 0 ? nullptr : (int*)host_status_slot();
   SEQM_REQUIRE(async_steps > 0 || hlive, "seqm_sp2_density: no page-locked status slot");

@@ -208,8 +208,6 @@ def test_force_end_to_end(name, path):
     dev = _dev()
     g = _load(name)
     sp = _params(g)
-    if sp['sp2'][0] and _mixed_sizes(g):
-        pytest.skip("SP2 on mixed-size batches: the reference's zero-padding quirk is not reproduced (DESIGN.md)")
     if path != 'host_loop' and (sp['sp2'][0] or int((4 * g['nHeavy'] + g['nHydro']).max()) > 32):
         pytest.skip("not eligible for the fused kernel; covered by host_loop")
     const = Constants().to(dev)

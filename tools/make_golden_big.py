@@ -65,7 +65,10 @@ def cases():
     sp, xyz = synth.mixed_organics(8, seed=3, min_atoms=5, max_atoms=14)
     out.append(dict(name='mixed8_PM3_eig', species=sp, coords=xyz, method='PM3', eps=1e-8, conv=[2, 0.0],
                     sp2=[False], eig=True))
-    sp, xyz = synth.water_cluster(500, seed=0)      # BASELINE.json configs[4]; the reference needs ~1 h of CPU
+    sp, xyz = synth.mixed_organics(8, seed=3, min_atoms=5, max_atoms=14)
+    out.append(dict(name='mixed8_PM3_sp2', species=sp, coords=xyz, method='PM3', eps=1e-6, conv=[2, 0.0],
+                    sp2=[True, 1e-5]))
+    sp, xyz = synth.water_cluster(500, seed=0)      # BASELINE.json configs[4]; the reference needs ~10 min of CPU (8 cores)
     out.append(dict(name='water500_PM3_sp2_c2', species=sp, coords=xyz, method='PM3', eps=1e-6, conv=[2, 0.0],
                     sp2=[True, 1e-5], slow=True))
     return out
