@@ -342,7 +342,7 @@ def run_c60xl(args, rank, world, local_rank):
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     par = dict(method='PM3', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[True, 1.0e-5], elements=[0, 6], learned=[],
-               pair_outer_cutoff=1.0e10)
+               pair_outer_cutoff=1.0e10, xl_cuda_graph=os.environ.get('SEQM_XL_GRAPH', '1') != '0')
     out = {'molid': [0], 'thermo': 10 ** 9, 'dump': 10 ** 9, 'prefix': '/tmp/seqm_b200_bench'}
     sp, xyz = synth.c60(nmol, seed=rank)
     species, coords = torch.as_tensor(sp).to(dev), torch.as_tensor(xyz).to(dev)

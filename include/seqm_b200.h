@@ -159,7 +159,8 @@ int seqm_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, 
  * steady-state loop such as MD or the later SCF iterations), then every two steps.
  * seqm_sp2_density_async: exactly `steps` (<= 64, rounded up to even) purification steps are enqueued, finished
  * molecules are skipped by their CTAs; no host synchronisation or allocation, so the call can be captured in a CUDA
- * graph; unfinished[0] (DEVICE int32) receives the number of molecules still live after the last step. */
+ * graph; the number of molecules still live after the last step is ADDED to unfinished[0] (DEVICE int32, a running
+ * total the caller zeroes and inspects when convenient). */
 size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize);
 int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
@@ -246,6 +247,32 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
  * the Pulay commutator; exported for tests).  ld even, stride in elements, active[batch] may be NULL. */
 int seqm_dgemm_batched(int64_t n, int64_t ld, const double* A, const double* B, double* C, int64_t stride,
                        int64_t batch, const uint8_t* active, void* stream);
+
+/* The elementwise half of an XL-BOMD / velocity-Verlet step (reference XLBOMD.py:277-307, MolecularDynamics.py:229-273),
+ * so that a whole MD step consists of launches of this library and can be captured in one CUDA graph.  Arithmetic in the
+ * order of the reference's tensor expressions, without FMA contraction.
+ *   seqm_xl_extrapolate   P = kappa D + sum_j coeff2m[cidx + j] Pt[j], Pt[m-1-cidx] = P with cidx = step % m
+ *                         (XLBOMD.py:293-295; coeff2m = the 2m doubled coefficients of :259-262, a HOST array);
+ *                         step from *step_dev (DEVICE int64, so one captured graph serves every step) or, if NULL,
+ *                         step_host.  nelem = elements of one density matrix batch (B n n); Pt[m][nelem].
+ *   seqm_verlet_kick_drift  v += 0.5 a dt ; x += v dt                    (n = 3 x atoms incl. padding)
+ *   seqm_verlet_finish    force = -gR ; a = force / mass * acc_scale ; v += 0.5 a dt ; (*step_dev)++ if not NULL;
+ *                         mass[n/3] per atom slot (1 for padding atoms)
+ *   seqm_energy_finish    Enuc[b] = sum of EnucAB over the pairs [pair_off[b], pair_off[b+1]) in a fixed order,
+ *                         Etot = Eelec + Enuc, Hf = Etot + hconst[b] (hconst = sum eheat - sum Eiso of the molecule:
+ *                         energy.py:92-94,109-118)
+ *   seqm_md_thermo        Ek[b], T[b] (MolecularDynamics.py:229-233) and, if P != NULL, atomic charges q[B][S] =
+ *                         tore - sum_mu P_mumu and dipole[B][3] = sum q x (:235-243) */
+int seqm_xl_extrapolate(int64_t nelem, int m, double kappa, const double* coeff2m, const int64_t* step_dev,
+                        int64_t step_host, const double* D, double* Pt, double* P, void* stream);
+int seqm_verlet_kick_drift(int64_t n, double dt, const double* acc, double* v, double* x, void* stream);
+int seqm_verlet_finish(int64_t n, double dt, double acc_scale, const double* gR, const double* mass, double* force,
+                       double* acc, double* v, int64_t* step_dev, void* stream);
+int seqm_energy_finish(int64_t nmol, const int32_t* pair_off, const double* EnucAB, const double* Eelec,
+                       const double* hconst, double* Enuc, double* Etot, double* Hf, void* stream);
+int seqm_md_thermo(int64_t nmol, int64_t molsize, double ke_scale, double ev_to_kelvin, const double* mass,
+                   const double* tore, const int32_t* natoms, const double* v, const double* x, const double* P,
+                   double* Ek, double* T, double* q, double* dipole, void* stream);
 
 #ifdef __cplusplus
 }

@@ -129,8 +129,41 @@ class XL_BOMD(Molecular_Dynamics_Basic):
     def get_force(self):
         pass
 
+    def _fused_step(self, const, step, mass, coordinates, velocities, species, acc, D, P, Pt, learned_parameters, kwargs):
+        """the XLStep object for this state, or None when the fused form does not apply"""
+        if not self.seqm_parameters.get('xl_fused', True) or const.do_timing or not coordinates.is_cuda:
+            return None
+        xs = getattr(self, '_xlstep', None)
+        if xs is not None and xs.matches(coordinates, velocities, acc, D, P, Pt) and xs.species is species:
+            if int(step) != xs.step0 + xs.nsteps:          # the caller jumped in the step count: follow it
+                xs.step_dev.fill_(int(step))
+                xs.step0 = int(step) - xs.nsteps
+                xs.graph = None
+            return xs
+        en = self.conservative_force.energy
+        prep = _engine.prepared_for(const, en.parser, en.packpar, species, coordinates, en.method, learned_parameters,
+                                    kwargs)
+        ok = all(torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float64 and t.is_contiguous()
+                 for t in (coordinates, velocities, acc, D, P, Pt))
+        if prep is None or not ok:
+            return None
+        from ._xlstep import XLStep
+        xs = XLStep(self, const, prep, species, coordinates, velocities, acc, D, P, Pt, mass, int(step),
+                    graph=bool(self.seqm_parameters.get('xl_cuda_graph', False)))
+        xs.species, xs.step0 = species, int(step)
+        self._xlstep = xs
+        return xs
+
     def one_step(self, const, step, mass, coordinates, velocities, species, acc, D, P, Pt, learned_parameters=dict(),
                  *args, **kwargs):
+        """pyseqm_b200: when the species-only data is cacheable the step runs as a fixed sequence of library launches on
+        the caller's state tensors, updated IN PLACE (_xlstep.XLStep; `xl_fused=False` in seqm_parameters restores the
+        autograd form below, `xl_cuda_graph=True` replays the step as one CUDA graph)."""
+        xs = None if args else self._fused_step(const, step, mass, coordinates, velocities, species, acc, D, P, Pt,
+                                                learned_parameters, kwargs)
+        if xs is not None:
+            Hf, force = xs.step()
+            return coordinates, velocities, acc, D, P, Pt, Hf, force
         dt = self.timestep
         t0 = _engine._tic(const)
         with torch.no_grad():

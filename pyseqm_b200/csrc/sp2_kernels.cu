@@ -87,6 +87,8 @@ constexpr int SP2_ROWS = 8;
 // an orbital of energy 0 that never couples: all npad = padm - m of them carry the same scalar xp = hN/(hN - h1), which
 // follows the branch decisions (xp^2 or 2 xp - xp^2) and enters tr X and tr X^2 with weight npad.  Tracking that scalar
 // reproduces the reference's bounds, branches and stopping step exactly without touching the matrices.
+__global__ void sp2_accumulate_kernel(const int* __restrict__ live, int32_t* __restrict__ total) { *total += *live; }
+
 __global__ void sp2_padmax_kernel(int nmol, const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro,
                                   const uint8_t* __restrict__ active, int* __restrict__ padm) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -828,7 +830,10 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
     cudaMemsetAsync(nlive, 0, SP2_NCOUNT * sizeof(int), st);
     for (int it = 0; it < nst && rc == SEQM_OK; ++it) enqueue(it);
     if (rc) return rc;
-    if (d_unfinished) SEQM_CUDA(cudaMemcpyAsync(d_unfinished, nlive + (nst - 1), sizeof(int), cudaMemcpyDeviceToDevice, st));
+    if (d_unfinished) {
+      sp2_accumulate_kernel<<<1, 1, 0, st>>>(nlive + (nst - 1), d_unfinished);
+      SEQM_CHECK_LAUNCH("sp2_accumulate_kernel");
+    }
   } else {
     int done = 0;
     int batch = g_sp2_hint.load();

@@ -15,8 +15,12 @@ torch.set_default_dtype(torch.float64)
 GMD = os.path.join(ROOT, 'tests', 'golden_md')
 
 
-@pytest.mark.parametrize('tag', ['bomd_eigh', 'xlbomd_sp2', 'xlbomd_eigh'])
-def test_md_trajectory(tag):
+@pytest.mark.parametrize('tag,mode', [('bomd_eigh', 'autograd'), ('xlbomd_sp2', 'fused'), ('xlbomd_sp2', 'graph'),
+                                      ('xlbomd_sp2', 'autograd'), ('xlbomd_eigh', 'fused'), ('xlbomd_eigh', 'graph'),
+                                      ('xlbomd_eigh', 'autograd')])
+def test_md_trajectory(tag, mode):
+    """mode (XL-BOMD only): 'fused' = the step as a fixed sequence of library launches (_xlstep.XLStep, the default),
+    'graph' = the same captured in one CUDA graph, 'autograd' = the reference-shaped form (EnergyXL + torch.autograd)"""
     from pyseqm_b200.MolecularDynamics import Molecular_Dynamics_Basic
     from pyseqm_b200.XLBOMD import XL_BOMD
     from pyseqm_b200.seqm_functions.constants import Constants
@@ -24,7 +28,8 @@ def test_md_trajectory(tag):
     g = np.load(os.path.join(GMD, tag + '.npz'))
     sp2 = g['sp2'].tolist()
     par = dict(method='AM1', scf_eps=1e-8, scf_converger=[2, 0.0], sp2=[bool(sp2[0])] + sp2[1:],
-               elements=[0, 1, 6, 8], learned=[], pair_outer_cutoff=1e10)
+               elements=[0, 1, 6, 8], learned=[], pair_outer_cutoff=1e10, xl_fused=(mode != 'autograd'),
+               xl_cuda_graph=(mode == 'graph'))
     out = {'molid': [0, 1], 'thermo': 1, 'dump': 10 ** 9, 'prefix': '/tmp/seqm_b200_md'}
     const = Constants().to(dev)
     if tag.startswith('xl'):
@@ -48,6 +53,11 @@ def test_md_trajectory(tag):
     assert np.abs(thermo - g['thermo']).max() < 2e-5 * max(1.0, np.abs(g['thermo']).max())
     assert np.abs(res[0].detach().cpu().numpy() - g['coords']).max() < 1e-7
     assert np.abs(res[1].detach().cpu().numpy() - g['vel']).max() < 1e-7
+    if tag.startswith('xl'):
+        xs = getattr(md, '_xlstep', None)
+        assert (xs is not None) == (mode != 'autograd')
+        if mode == 'graph':
+            assert xs.graph is not None and xs.nsteps == int(g['steps'])
 
 
 def test_standalone_ops_match_oracle():
