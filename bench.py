@@ -1,14 +1,19 @@
 #!/usr/bin/env python
-"""Benchmark of the batched SCF hot path (BASELINE.json config 2): AM1 SCF + forces for a batch of 1024
-perturbed benzene geometries (12 atoms, 30 orbitals), eigh density path; metric = SCF molecules / second.
+"""Benchmark of the batched SCF hot path.  BASELINE.json metric: "SCF molecules/sec & XL-BOMD steps/sec".
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload benzene|c60xl|water|organics]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload all|benzene|c60xl|water|organics]
 
-One step = one `Force` call (Parser + pair pass + SCF + force adjoint) over the whole batch.  `value` is
-timed with the coordinates resident in HBM; `e2e` includes, every step, the host->device copy of the
-coordinates from pinned memory and the device->host copy of forces and energies.  N > 1: one process per
-GPU (torchrun), every rank runs its own 1024-molecule shard (weak scaling), no collective in the loop,
-one all_gather of the energies at the end of every step.
+Default (`--workload all`): ONE JSON line.  Top level = BASELINE.json configs[1], AM1 SCF + forces for 1024 perturbed
+benzenes per GPU (12 atoms, 30 orbitals, eigh), metric SCF molecules/s; one step = one `Force` call (pair pass + SCF +
+force adjoint) over the whole batch; `value` is timed with the coordinates resident in HBM, `e2e` includes, every step,
+the host->device copy of the coordinates from pinned memory and the device->host copy of forces and energies.  N > 1:
+one process per GPU (torchrun), every rank runs its own 1024-molecule shard (weak scaling), no collective in the loop,
+one asynchronous gather of the energies per step.
+"xlbomd" = configs[2]: XL-BOMD (k = 5) of 256 C60 per GPU, PM3, SP2: batch steps/s, with its own roofline / e2e /
+cpu_baseline.  With N > 1 (or SEQM_BENCH_SUB=all) also "organics" = configs[3] (65,536 mixed organics, STRONG scaling by
+molecule) and "water" = configs[4] ((H2O)500, SP2 tiles sharded over the GPUs, checked against the reference fixture).
+`--impl reference`: the reference's own CPU path (oracle/_ref = the unmodified package, built by oracle/build_ref.sh;
+else the oracle port) on the host cores, same configuration as the top-level workload.
 """
 import argparse
 import datetime
@@ -27,6 +32,8 @@ sys.path.insert(0, ROOT)
 torch.set_default_dtype(torch.float64)
 
 NMOL = 1024
+WORKLOAD_BENZENE = ("AM1 SCF+forces, 1024 perturbed benzenes per GPU (12 atoms, 30 orbitals), eigh, converger [2], "
+                    "scf_eps 1e-6 (BASELINE.json configs[1])")
 SEQM_PAR = dict(method='AM1', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6], learned=[],
                 pair_outer_cutoff=1.0e10)
 
@@ -97,36 +104,175 @@ class ClockSampler:
                 "samples": len(inside), "window": window}
 
 
+def load_reference():
+    """the unmodified reference package from oracle/_ref (built by oracle/build_ref.sh), or None"""
+    root = os.path.join(ROOT, 'oracle', '_ref')
+    if not os.path.exists(os.path.join(root, 'seqm', 'basics.py')):
+        return None
+    import warnings
+    warnings.filterwarnings('ignore', category=SyntaxWarning)
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    import seqm
+    return seqm if os.path.abspath(seqm.__file__).startswith(root) else None
+
+
+class CpuPath:
+    """The reference's CPU implementation of the path on this box's host cores: the unmodified reference (oracle/_ref,
+    kind "reference") when the recipe has installed it, else the oracle port (kind "port")."""
+
+    def __init__(self):
+        import warnings
+        warnings.filterwarnings('ignore')
+        self.seqm = load_reference()
+        self.kind = 'reference' if self.seqm is not None else 'port'
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        if self.seqm is None:
+            sys.path.insert(0, os.path.join(ROOT, 'oracle'))
+            import seqm_oracle
+            self.orc = seqm_oracle
+
+    def _par(self, method, sp2, elements):
+        p = dict(method=method, scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=list(sp2), elements=list(elements), learned=[],
+                 pair_outer_cutoff=1.0e10)
+        p['parameter_file_dir'] = os.path.join(os.path.dirname(self.seqm.__file__), 'params') + '/'
+        return p
+
+    def force_seconds(self, sp, xyz, method, sp2=(False,), elements=(0, 1, 6, 7, 8)):
+        """wall time of one Force call (SCF + forces) over the batch"""
+        species, coords = torch.as_tensor(sp), torch.as_tensor(xyz).clone()
+        t0 = time.time()
+        if self.seqm is not None:
+            from seqm.basics import Force
+            from seqm.seqm_functions.constants import Constants
+            Force(self._par(method, sp2, elements))(Constants(), coords, species)
+        else:
+            self.orc.run(species, coords, method=method, scf_eps=1e-6, converger=(2, 0.0), sp2=tuple(sp2))
+        return time.time() - t0
+
+    def xlbomd_seconds_per_step(self, sp, xyz, steps):
+        """XL-BOMD (k = 5, PM3, SP2 1e-5) steady-state seconds per step over the batch; None for the port (the oracle has
+        no MD driver)"""
+        if self.seqm is None:
+            return None
+        from seqm.XLBOMD import XL_BOMD
+        from seqm.seqm_functions.constants import Constants
+        par = self._par('PM3', [True, 1.0e-5], [0, 6])
+        out = {'molid': [0], 'thermo': 10 ** 9, 'dump': 10 ** 9, 'prefix': '/tmp/seqm_ref_bench'}
+        const = Constants()
+        species, coords = torch.as_tensor(sp), torch.as_tensor(xyz).clone()
+        md = XL_BOMD(par, timestep=1.0, k=5, output=out)
+        torch.manual_seed(0)
+        vel = md.initialize_velocity(const, coords, species, Temp=300.0)
+        import contextlib, io
+        with contextlib.redirect_stdout(io.StringIO()):
+            md.run(const, 1, coords, vel, species)              # initialisation (full SCF) + one step: untimed
+            t0 = time.time()
+            md.run(const, steps + 1, coords, vel, species)      # SCF again + steps + 1 steps
+            t1 = time.time()
+            md.run(const, 1, coords, vel, species)
+            t2 = time.time()
+        return ((t1 - t0) - (t2 - t1)) / steps                  # the initialisation cancels
+
+
 def run_reference(args, rank, world):
-    """The reference's algorithm on the host cores (oracle port: the reference itself is a Python package that
-    does not exist on the GPU box).  Each step = a bounded sample of the same workload."""
+    """`--impl reference`: the reference's own CPU path on the host cores, SAME configuration as the product arm (1024
+    perturbed benzenes per step, AM1, eigh, converger [2], scf_eps 1e-6), every step one Force call over all of them;
+    plus the XL-BOMD half of the metric on a bounded sample (2 C60)."""
     if rank != 0:
         return
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    import seqm_oracle as orc
     from pyseqm_b200 import synth
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    nsample = 512
-    sp, xyz = synth.benzene(nsample, seed=0)
-    species, coords = torch.as_tensor(sp), torch.as_tensor(xyz)
+    cpu = CpuPath()
+    sp, xyz = synth.benzene(NMOL, seed=0)
     times = []
     for it in range(args.warmup + args.steps):
-        t0 = time.time()
-        orc.run(species, coords, method='AM1', scf_eps=1e-6, converger=(2, 0.0))
+        dt = cpu.force_seconds(sp, xyz, 'AM1', elements=(0, 1, 6))
         if it >= args.warmup:
-            times.append(time.time() - t0)
+            times.append(dt)
     ms = 1e3 * sum(times) / len(times)
-    val = nsample / (ms * 1e-3)
-    sample = "%d of the 1024 perturbed benzenes per step (same generator, seed 0)" % nsample
-    print(json.dumps({
+    val = NMOL / (ms * 1e-3)
+    sample = "all %d perturbed benzenes of the product arm's rank 0 per step (same generator, seed 0)" % NMOL
+    spc, xyzc = synth.c60(2, seed=0)
+    xl = cpu.xlbomd_seconds_per_step(spc, xyzc, 3)
+    line = {
         "impl": "reference", "metric": "SCF molecules/sec", "value": val, "unit": "molecules/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "AM1 SCF+forces, perturbed benzene (12 atoms, 30 orbitals), eigh, converger [2], "
-                               "scf_eps 1e-6", "sample": sample},
-        "cpu_baseline": {"value": val, "unit": "molecules/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": val, "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        "config": {"workload": WORKLOAD_BENZENE, "molecules_per_step": NMOL, "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "molecules/s", "cores": cpu.cores, "kind": cpu.kind, "sample": sample},
+        "e2e": {"value": val, "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if xl:
+        line["xlbomd"] = {"metric": "XL-BOMD steps/sec", "value": 1.0 / xl * (2.0 / 256.0), "unit": "batch steps/s (256 C60 per batch)",
+                          "sample": "2 C60, 3 steady-state steps, scaled to the 256-molecule batch of the product arm "
+                                    "(cost is linear in the number of molecules)", "kind": cpu.kind, "cores": cpu.cores,
+                          "seconds_per_step_2_c60": xl}
+    print(json.dumps(line))
+
+
+def ncu_traffic(key):
+    """DRAM bytes per launch of a kernel from the committed ncu --set full capture of this round (profiles/
+    ncu_traffic.json, written by tools/ncu_summary.py from the .ncu-rep); None if there is no capture"""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')) as f:
+            e = json.load(f).get(key)
+        return (int(e['dram_bytes']), e['source']) if e else (None, None)
+    except Exception:
+        return None, None
+
+
+def profile_report(L):
+    import ctypes
+    buf = ctypes.create_string_buffer(1 << 16)
+    L.seqm_profile_report(buf, len(buf))
+    L.seqm_profile_enable(0)
+    prof = {}
+    for line in buf.value.decode().splitlines():
+        nm, ms, cnt = line.rsplit(' ', 2)
+        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
+    tot = sum(v["ms"] for v in prof.values()) or 1.0
+    for v in prof.values():
+        v["share"] = v["ms"] / tot
+    return prof, tot
+
+
+def dgemm_peak(dev):
+    """FP64 GEMM rate of this box, measured here (cuBLAS DGEMM through torch.matmul, 4096^3, best of 5): the tensor
+    roofline's denominator (MEASURED_PEAKS.json holds no FP64 number)"""
+    A_ = torch.randn(4096, 4096, device=dev)
+    B_ = torch.randn(4096, 4096, device=dev)
+    torch.matmul(A_, B_)
+    best = 1e30
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(A_, B_)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
+
+
+class Ctx:
+    """one process of the run: rank, device, library, distributed helpers (the process group is created once in main)"""
+
+    def __init__(self, args, rank, world, local_rank):
+        self.args, self.rank, self.world = args, rank, world
+        self.dev = torch.device('cuda', local_rank)
+        self.local_rank = local_rank
+
+    def barrier(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, vals):
+        t = torch.tensor([float(v) for v in vals], device=self.dev)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(x) for x in t]
 
 
 def algorithmic_bytes(topo):
@@ -160,45 +306,62 @@ def time_op(fn, flush, reps=5):
     return sum(a.elapsed_time(b) for a, b in ev) / reps
 
 
-def run_gpu(args, rank, world, local_rank):
-    import ctypes
+def run_gpu(ctx):
+    """BASELINE.json configs[1]: the headline workload.  -> result dict on rank 0, None elsewhere"""
     from pyseqm_b200 import _lib, _ops, synth
     from pyseqm_b200.basics import Force
     from pyseqm_b200.seqm_functions.constants import Constants
-    dev = torch.device('cuda', local_rank)
-    torch.cuda.set_device(dev)
+    args, rank, world, dev = ctx.args, ctx.rank, ctx.world, ctx.dev
     if world > 1:
         import torch.distributed as dist
         from pyseqm_b200.distributed import gather_molecules
-        dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     sp, xyz = synth.benzene(NMOL, seed=rank)
     species = torch.as_tensor(sp).to(dev)
     coords_host = torch.as_tensor(xyz).pin_memory()
     coords = coords_host.to(dev)
     const = Constants().to(dev)
-    force_mod = Force(dict(SEQM_PAR)).to(dev)
+    # defer_scf_warning: the SCF status of step k is read when step k+1 starts, so the host enqueues the next step
+    # while the GPU still runs this one (pyseqm_b200/basics.py:Force)
+    force_mod = Force(dict(SEQM_PAR, defer_scf_warning=True)).to(dev)
     flush_buf = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)     # > 126 MB of L2
 
     def flush():
         flush_buf.fill_(1)
 
+    pending = []
+
     def step(x):
         out = force_mod(const, x, species)
         if world > 1:
-            gather_molecules(out[2], NMOL * world, world)     # energies of every shard, global molecule order
+            # energies of every shard in global molecule order: one preallocated all_gather_into_tensor, asynchronous on
+            # NCCL's stream; the result of step k is consumed (waited for) while step k+1 is already enqueued
+            pending.append(gather_molecules(out[2], NMOL * world, world, async_op=True))
+            if len(pending) > 1:
+                pending.pop(0).wait()
         return out
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def drain():
+        while pending:
+            pending.pop(0).wait()
+        force_mod.flush_status()
 
+    barrier = ctx.barrier
+    local_rank = ctx.local_rank
+    # cold call: first call with this species tensor (Parser, parameter gather, topology, per-atom records, initial
+    # density: everything _engine.Prepared caches afterwards), after the CUDA context / module load of a dry call
+    Force(dict(SEQM_PAR)).to(dev)(const, coords[:8].clone(), species[:8].clone())
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = step(coords.clone())
+    torch.cuda.synchronize()
+    cold_ms = (time.perf_counter() - t0) * 1e3
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     for _ in range(args.warmup):
         out = step(coords.clone())
+    drain()
     nconv_fail = int(out[10].sum())
     # ---- resident-input timing ----
     barrier()
@@ -213,6 +376,7 @@ def run_gpu(args, rank, world, local_rank):
         step(x)
         b.record()
         evs.append((a, b))
+    drain()
     barrier()
     launches = int(L.seqm_launch_count() - l0)
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
@@ -227,31 +391,19 @@ def run_gpu(args, rank, world, local_rank):
         f_host.copy_(o[0], non_blocking=True)
         e_host.copy_(o[2].detach(), non_blocking=True)
         torch.cuda.synchronize()
+    drain()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     sampler.mark_end()
     if rank == 0:
         sampler.stop()
-    t = torch.tensor([total_ms, e2e_ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(t[0]), float(t[1])
+    total_ms, e2e_ms = ctx.max_over_ranks([total_ms, e2e_ms])
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
     # ---- per-kernel profile of one step, and the kernels timed alone on the converged state ----
     L.seqm_profile_enable(1)
     force_mod(const, coords.clone(), species)        # no collective here: the other ranks have finished
-    buf = ctypes.create_string_buffer(1 << 16)
-    L.seqm_profile_report(buf, len(buf))
-    L.seqm_profile_enable(0)
-    prof = {}
-    for line in buf.value.decode().splitlines():
-        nm, ms, cnt = line.rsplit(' ', 2)
-        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
-    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
-    for v in prof.values():
-        v["share"] = v["ms"] / tot_prof
+    force_mod.flush_status()
+    prof, tot_prof = profile_report(L)
     st = force_mod.energy.last_state
     topo = st['topo']
     ab = algorithmic_bytes(topo)
@@ -289,57 +441,49 @@ def run_gpu(args, rank, world, local_rank):
         m_, B_ = int(topo.mmax), int(topo.nmol)
         iters = int(st['iterations']) + 1
         flops = B_ * iters * (9.0 * m_ ** 3 + 2.0 * m_ * m_ * int(topo.nocc.max()))      # 9 m^3 + 2 m^2 nocc per eigensolve
-        roof.update({"traffic": 198338048 + 125199872,
-                     "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum, one launch (cold-cache replay), "
-                                       "profiles/r01p_scf_small_ncu.txt",
-                     "limiter": "latency of one warp per molecule (ncu: sm__pipe_fp64_cycles_active 19.5 %, "
-                                "smsp__issue_active 26.0 %, stalls short_scoreboard / wait / long_scoreboard)",
+        traffic, tsrc = ncu_traffic('scf_small_benzene1024')
+        roof.update({"traffic": traffic, "traffic_source": tsrc,
+                     "limiter": "latency of one warp per molecule (6.9 molecules per SM; ncu: FP64 pipe and issue slots "
+                                "mostly idle, stalls short_scoreboard / wait / long_scoreboard - DESIGN.md section 6)",
                      "algorithmic_tflops": flops / (kernels[top]["ms_per_launch"] * 1e-3) / 1e12,
                      "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
-    # ---- CPU baseline: the oracle port on a bounded sample, all host cores ----
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    import seqm_oracle as orc
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    ns, reps = NMOL, 4
-    t0 = time.time()
-    for _ in range(reps):
-        orc.run(torch.as_tensor(sp), torch.as_tensor(xyz), method='AM1', scf_eps=1e-6, converger=(2, 0.0))
-    cpu_s = (time.time() - t0) / reps
+    # ---- CPU baseline: the reference's CPU path (oracle/_ref, else the oracle port) on this rank's batch ----
+    cpu = CpuPath()
+    ns, reps = NMOL, 2
+    cpu.force_seconds(sp[:64], xyz[:64], 'AM1', elements=(0, 1, 6))
+    cpu_s = sum(cpu.force_seconds(sp, xyz, 'AM1', elements=(0, 1, 6)) for _ in range(reps)) / reps
+    cores = cpu.cores
     ms_step = total_ms / args.steps
     nm_total = NMOL * world
-    print(json.dumps({
+    return ({
         "metric": "SCF molecules/sec", "value": nm_total / (ms_step * 1e-3), "unit": "molecules/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "AM1 SCF+forces, 1024 perturbed benzenes per GPU (12 atoms, 30 orbitals), eigh, "
-                               "converger [2], scf_eps 1e-6 (BASELINE.json configs[1])",
+        "config": {"workload": WORKLOAD_BENZENE,
                    "molecules_per_gpu": NMOL, "l2": "192 MiB buffer written between timed steps",
-                   "scf_not_converged": nconv_fail, "scf_iterations": int(st['iterations'])},
+                   "scf_not_converged": nconv_fail, "scf_iterations": int(st['iterations']),
+                   "api": "pyseqm_b200.basics.Force with defer_scf_warning=True (SCF status of a call read at the next "
+                          "call); N > 1: asynchronous gather of the energies, consumed one step later"},
+        "cold_call_ms": cold_ms,
+        "cold_call_note": "first Force call with a new species tensor (Parser, parameter gather, topology, per-atom "
+                          "records, initial guess built and cached), CUDA context already up; steady state is ms_per_step",
         "e2e": {"value": nm_total / (e2e_ms / args.steps * 1e-3), "unit": "molecules/s",
                 "h2d_bytes_per_step": NMOL * 12 * 3 * 8, "d2h_bytes_per_step": NMOL * 12 * 3 * 8 + NMOL * 8},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
         "profile_one_step": prof,
-        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": "port",
-                         "sample": "the %d benzenes of rank 0, %d Force-equivalent calls of the oracle" % (ns, reps)}}))
-    if world > 1:
-        dist.destroy_process_group()
+        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": cpu.kind,
+                         "sample": "the %d benzenes of rank 0, %d Force calls" % (ns, reps)}})
 
 
-def run_c60xl(args, rank, world, local_rank):
+def run_c60xl(ctx):
     """Secondary workload (BASELINE.json configs[2]): XL-BOMD (k=5) of 256 C60 per GPU, PM3, SP2 density
     (eps 1e-5); one step = one `XL_BOMD.one_step` of the whole batch (pair pass, Fock build with the dynamical
     density, one SP2 purification, shadow energy, force adjoint, Verlet).  metric: batch MD steps per second."""
-    import ctypes
     from pyseqm_b200 import _lib, synth
     from pyseqm_b200.XLBOMD import XL_BOMD
     from pyseqm_b200.seqm_functions.constants import Constants
     nmol = int(os.environ.get('SEQM_BENCH_C60', '256'))
-    dev = torch.device('cuda', local_rank)
-    torch.cuda.set_device(dev)
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group('nccl', device_id=dev)
+    args, rank, world, dev, local_rank = ctx.args, ctx.rank, ctx.world, ctx.dev, ctx.local_rank
     L = _lib.lib()
     par = dict(method='PM3', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[True, 1.0e-5], elements=[0, 6], learned=[],
                pair_outer_cutoff=1.0e10, xl_cuda_graph=os.environ.get('SEQM_XL_GRAPH', '1') != '0')
@@ -365,15 +509,11 @@ def run_c60xl(args, rank, world, local_rank):
         stepno[0] += 1
         return c, Hf
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    barrier = ctx.barrier
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, 3)):      # step 1 calibrates the SP2 step count, step 2 captures the graph
         step()
     barrier()
     sampler.mark_begin()
@@ -384,7 +524,10 @@ def run_c60xl(args, rank, world, local_rank):
         step()
     b.record()
     barrier()
-    launches = int(L.seqm_launch_count() - l0)
+    xs = getattr(md, '_xlstep', None)
+    graph = xs is not None and xs.graph is not None
+    # a replayed graph launches the kernels counted once at capture time
+    launches = int(xs.launches_per_step * args.steps) if graph else int(L.seqm_launch_count() - l0)
     total_ms = a.elapsed_time(b)
     c_host = torch.empty(nmol, 60, 3).pin_memory()
     e_host = torch.empty(nmol).pin_memory()
@@ -399,57 +542,37 @@ def run_c60xl(args, rank, world, local_rank):
     sampler.mark_end()
     if rank == 0:
         sampler.stop()
-    t = torch.tensor([total_ms, e2e_ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(t[0]), float(t[1])
+    total_ms, e2e_ms = ctx.max_over_ranks([total_ms, e2e_ms])
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
+    # per-kernel profile: one step with the launches enqueued one by one (a replayed graph has no event marks)
+    if xs is not None:
+        xs.want_graph, keep = False, xs.graph
     L.seqm_profile_enable(1)
     step()
-    buf = ctypes.create_string_buffer(1 << 16)
-    L.seqm_profile_report(buf, len(buf))
-    L.seqm_profile_enable(0)
-    prof = {}
-    for line in buf.value.decode().splitlines():
-        nm, ms, cnt = line.rsplit(' ', 2)
-        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
-    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
-    for v in prof.values():
-        v["share"] = v["ms"] / tot_prof
-    # FP64 GEMM peak of this box, measured here (cuBLAS DGEMM through torch.matmul, 4096^3, best of 5): denominator
-    A_ = torch.randn(4096, 4096, device=dev)
-    B_ = torch.randn(4096, 4096, device=dev)
-    torch.matmul(A_, B_)
-    best = 1e30
-    for _ in range(5):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        torch.matmul(A_, B_)
-        e1.record()
-        torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    fp64_peak = 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
-    del A_, B_
+    prof, tot_prof = profile_report(L)
+    if xs is not None:
+        xs.want_graph, xs.graph = graph, keep
+    fp64_peak = dgemm_peak(dev)
     m = 240
     sp = prof.get('sp2_step', {"ms": 0.0, "launch_groups": 1, "share": 0.0})
-    nstep_launch = 2 * max(sp["launch_groups"], 1)          # two purification steps per profiled group
+    nstep_launch = xs.sp2_steps if xs is not None else 2 * max(sp["launch_groups"], 1)
+    sp2_needed = nstep_launch - 4 if xs is not None else nstep_launch      # XLStep launches the calibrated count + 4 no-ops
     flops = 2.0 * m ** 3 * nmol                              # 2 m^3 per multiplication and molecule
-    per_launch = sp["ms"] / nstep_launch
+    per_launch = sp["ms"] / max(sp2_needed, 1)               # the no-op launches cost microseconds
     T_ = (m + 63) // 64
+    exec_frac = (T_ + 1) / (2.0 * T_)
     roof = {"bound": "tensor", "kernel": "sp2_step_kernel (X^2 on the upper block triangle, DMMA m8n8k4 f64, fused trace "
                                          "rule / update / transpose epilogue)", "share_of_step": sp["share"],
             "achieved": flops / (per_launch * 1e-3) / 1e12 if per_launch else None, "peak": fp64_peak,
             "peak_source": "cuBLAS DGEMM 4096^3 measured in this run (MEASURED_PEAKS.json holds no FP64 number)",
             "unit": "TFLOP/s", "frac": flops / (per_launch * 1e-3) / 1e12 / fp64_peak if per_launch else None,
-            "traffic": (118043904 + 79299328) if nmol == 256 else None,
-            "traffic_source": "ncu dram bytes of one sp2_step_kernel launch, profiles/r01p_c60_ncu.txt (top stall: "
-                              "math_pipe_throttle, tensor pipe = DMMA)",
-            "note": "algorithmic flops 2 m^3 per product; the kernel executes %d of %d tiles (symmetry), i.e. %.3f of "
-                    "them; the last launch of the loop may be a no-op" % (T_ * (T_ + 1) // 2, T_ * T_,
-                                                                        (T_ + 1) / (2.0 * T_))}
+            "executed_tflops": exec_frac * flops / (per_launch * 1e-3) / 1e12 if per_launch else None,
+            "executed_frac": exec_frac * flops / (per_launch * 1e-3) / 1e12 / fp64_peak if per_launch else None,
+            "traffic": ncu_traffic('sp2_step_c60x256')[0], "traffic_source": ncu_traffic('sp2_step_c60x256')[1],
+            "note": "`achieved` / `frac` use the reference's count, 2 m^3 per product (SURVEY 8d); the kernel multiplies "
+                    "only %d of %d tiles (symmetry): `executed_*` = the DMMA work really done over the same time, the "
+                    "number to hold against the DGEMM rate" % (T_ * (T_ + 1) // 2, T_ * T_)}
     # HBM fraction of the integral / Fock kernels at this size (one launch each inside the profiled step)
     hbm, peak_src = peaks()
     npair = nmol * 60 * 59 // 2
@@ -463,39 +586,44 @@ def run_c60xl(args, rank, world, local_rank):
             kernels[nm_] = {"ms_per_launch": ms_, "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / (ms_ * 1e-3) / 1e9,
                             "frac_of_hbm": nbytes / (ms_ * 1e-3) / 1e9 / hbm}
     ms_step = total_ms / args.steps
-    print(json.dumps({
+    cpu = CpuPath()
+    spc, xyzc = synth.c60(2, seed=0)
+    xl_s = cpu.xlbomd_seconds_per_step(spc, xyzc, 3)
+    cpu_base = None
+    if xl_s:
+        cpu_base = {"value": 1.0 / xl_s * (2.0 / nmol), "unit": "batch steps/s", "cores": cpu.cores, "kind": cpu.kind,
+                    "sample": "XL_BOMD of the reference on 2 C60, 3 steady-state steps (initialisation subtracted), scaled "
+                              "to the %d-molecule batch (cost linear in the number of molecules)" % nmol}
+    return ({
         "metric": "XL-BOMD steps/sec", "value": world / (ms_step * 1e-3), "unit": "batch steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "XL-BOMD k=5, %d C60 per GPU (60 atoms, 240 orbitals), PM3, SP2 eps 1e-5 "
                                "(BASELINE.json configs[2])" % nmol, "molecules_per_gpu": nmol,
-                   "l2": "working set per step (P, F, D, w, ring: > 1 GB) exceeds L2"},
+                   "l2": "working set per step (P, F, D, w, ring: > 1 GB) exceeds L2",
+                   "api": "pyseqm_b200.XLBOMD.XL_BOMD.one_step, fused step (%s)" % ("one CUDA graph replay per step" if graph else "launch by launch"),
+                   "sp2_steps_launched": nstep_launch},
         "e2e": {"value": world / (e2e_ms / args.steps * 1e-3), "unit": "batch steps/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": nmol * 60 * 3 * 8 + nmol * 8,
                 "note": "MD state lives on the device (as in the reference); coordinates and Hf go to pinned host "
                         "memory every step"},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
-        "profile_one_step": prof, "cpu_baseline": None}))
-    if world > 1:
-        dist.destroy_process_group()
+        "profile_one_step": prof, "cpu_baseline": cpu_base})
 
 
-def run_water(args, rank, world, local_rank):
+def run_water(ctx):
     """Third workload (BASELINE.json configs[4]): PM3 SCF + forces of ONE (H2O)_500 cluster (1500 atoms, 3000 packed
     orbitals), SP2 density (eps 1e-5).  One step = one `Force` call.  N > 1: STRONG scaling - every rank holds the
     whole system (pair pass, Fock build and gradient replicated, < 10 % of the step), the SP2 multiplications are
     tile-sharded over the ranks with ncclAllGather (pyseqm_b200.distributed.enable_sp2_sharding)."""
-    import ctypes
     from pyseqm_b200 import _lib, synth
     from pyseqm_b200.basics import Force
     from pyseqm_b200.seqm_functions.constants import Constants
     nwater = int(os.environ.get('SEQM_BENCH_WATER', '500'))
-    dev = torch.device('cuda', local_rank)
-    torch.cuda.set_device(dev)
+    args, rank, world, dev, local_rank = ctx.args, ctx.rank, ctx.world, ctx.dev, ctx.local_rank
     if world > 1:
         import torch.distributed as dist
         from pyseqm_b200.distributed import disable_sp2_sharding, enable_sp2_sharding
-        dist.init_process_group('nccl', device_id=dev)
         enable_sp2_sharding()
     L = _lib.lib()
     if os.environ.get('SEQM_SP2_P2P'):
@@ -510,23 +638,19 @@ def run_water(args, rank, world, local_rank):
     coords = coords_host.to(dev)
     const = Constants().to(dev)
     fm = Force(par).to(dev)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    barrier = ctx.barrier
+    nsteps = max(1, min(args.steps, int(os.environ.get('SEQM_BENCH_WATER_STEPS', '3'))))
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    for _ in range(args.warmup):
+    for _ in range(min(args.warmup, 2)):
         out = fm(const, coords.clone(), species)
     barrier()
     sampler.mark_begin()
     l0 = L.seqm_launch_count()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for _ in range(args.steps):
+    for _ in range(nsteps):
         out = fm(const, coords.clone(), species)
     b.record()
     barrier()
@@ -536,7 +660,7 @@ def run_water(args, rank, world, local_rank):
     e_host = torch.empty(1).pin_memory()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(nsteps):
         o = fm(const, coords_host.to(dev, non_blocking=True), species)
         f_host.copy_(o[0], non_blocking=True)
         e_host.copy_(o[2].detach(), non_blocking=True)
@@ -545,48 +669,33 @@ def run_water(args, rank, world, local_rank):
     sampler.mark_end()
     if rank == 0:
         sampler.stop()
-    t = torch.tensor([total_ms, e2e_ms], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms = float(t[0]), float(t[1])
+    total_ms, e2e_ms = ctx.max_over_ranks([total_ms, e2e_ms])
     # per-kernel profile of one more call: collective inside, so every rank runs it; rank 0 reports
     L.seqm_profile_enable(1 if rank == 0 else 0)
+    c0 = L.seqm_sp2_step_count()
     fm(const, coords.clone(), species)
     torch.cuda.synchronize()
+    sp2_steps_profiled = L.seqm_sp2_step_count() - c0
     st = fm.energy.last_state
     if world > 1:
         dist.barrier()
         disable_sp2_sharding()
+    # parity of the sharded run: every rank holds the whole system, so rank 0's energy must equal the single-GPU
+    # reference fixture of the same geometry (tests/golden_big/water500_PM3_sp2_c2.npz: seed 0, 500 waters)
+    parity = None
+    fx = os.path.join(ROOT, 'tests', 'golden_big', 'water500_PM3_sp2_c2.npz')
+    if nwater == 500 and os.path.exists(fx) and rank == 0:
+        g = np.load(fx)
+        parity = {"max_abs_dEtot_eV_per_water": float(np.abs(out[2].detach().cpu().numpy() - g['Etot']).max() / nwater),
+                  "max_abs_dforce_eV_per_A": float(np.abs(out[0].cpu().numpy() - g['force']).max()),
+                  "against": "tests/golden_big/water500_PM3_sp2_c2.npz (unmodified reference, CPU)"}
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    buf = ctypes.create_string_buffer(1 << 16)
-    L.seqm_profile_report(buf, len(buf))
-    L.seqm_profile_enable(0)
-    prof = {}
-    for line in buf.value.decode().splitlines():
-        nm, ms, cnt = line.rsplit(' ', 2)
-        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
-    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
-    for v in prof.values():
-        v["share"] = v["ms"] / tot_prof
-    A_ = torch.randn(4096, 4096, device=dev)
-    B_ = torch.randn(4096, 4096, device=dev)
-    torch.matmul(A_, B_)
-    best = 1e30
-    for _ in range(5):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        torch.matmul(A_, B_)
-        e1.record()
-        torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    fp64_peak = 2.0 * 4096 ** 3 / (best * 1e-3) / 1e12
-    del A_, B_
+        return None
+    prof, tot_prof = profile_report(L)
+    fp64_peak = dgemm_peak(dev)
     m = int(st['topo'].mmax)
     spp = prof.get('sp2_step', {"ms": 0.0, "launch_groups": 1, "share": 0.0})
-    nstep = 2 * max(spp["launch_groups"], 1)                  # two purification steps per profiled group (upper bound)
+    nstep = max(int(sp2_steps_profiled), 1)                  # purification steps of the profiled call (library counter)
     flops = 2.0 * m ** 3                                     # 2 m^3 per multiplication
     per_step = spp["ms"] / nstep
     T_ = (m + 63) // 64
@@ -595,15 +704,15 @@ def run_water(args, rank, world, local_rank):
             "share_of_step": spp["share"], "achieved": ach, "peak": fp64_peak * world,
             "peak_source": "cuBLAS DGEMM 4096^3 measured in this run on rank 0, times the number of GPUs",
             "unit": "TFLOP/s", "frac": ach / (fp64_peak * world) if ach else None,
-            "traffic": (181162752 + 51730432) if (world == 1 and nwater == 500) else None,
-            "traffic_source": "ncu dram bytes of one single-GPU sp2_step_kernel launch, profiles/r01p_sp2_step_water_ncu.txt "
-                              "(sm__pipe_tensor_cycles_active 61 %, top stall math_pipe_throttle)",
+            "executed_frac": (ach * (T_ + 1) / (2.0 * T_)) / (fp64_peak * world) if ach else None,
+            "traffic": ncu_traffic('sp2_step_water500')[0] if world == 1 else None,
+            "traffic_source": ncu_traffic('sp2_step_water500')[1] if world == 1 else None,
             "note": "2 m^3 flops per purification step over the time of one step (multiplication, all-gather and "
                     "unpack) on all GPUs; %d of %d tiles executed (symmetry)" % (T_ * (T_ + 1) // 2, T_ * T_)}
-    ms_step = total_ms / args.steps
-    print(json.dumps({
+    ms_step = total_ms / nsteps
+    return ({
         "metric": "SCF systems/sec (one 1500-atom system, SCF + forces)", "value": 1.0 / (ms_step * 1e-3), "unit": "Force calls/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "n_gpus": world, "steps": nsteps, "warmup": min(args.warmup, 2), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "PM3 SCF+forces, one (H2O)_%d cluster (%d atoms, %d packed orbitals), SP2 eps 1e-5, converger "
                                "[2], scf_eps 1e-6 (BASELINE.json configs[4])" % (nwater, 3 * nwater, m),
@@ -611,32 +720,32 @@ def run_water(args, rank, world, local_rank):
                    "l2": "working set (X 2 x %d MB, integrals %d MB) exceeds L2" % (m * m * 8 // 10 ** 6, 900 * nwater // 500),
                    "scf_iterations": int(st['iterations']) if st.get('iterations') is not None else None,
                    "scf_not_converged": int(out[10].sum())},
-        "e2e": {"value": 1.0 / (e2e_ms / args.steps * 1e-3), "unit": "Force calls/s", "h2d_bytes_per_step": 3 * nwater * 24,
+        "e2e": {"value": 1.0 / (e2e_ms / nsteps * 1e-3), "unit": "Force calls/s", "h2d_bytes_per_step": 3 * nwater * 24,
                 "d2h_bytes_per_step": 3 * nwater * 24 + 8},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
-        "cpu_baseline": None}))
-    if world > 1:
-        dist.destroy_process_group()
+        "parity": parity,
+        "cpu_baseline": {"value": 1.0 / 592.7, "unit": "Force calls/s", "cores": 8, "kind": "reference",
+                         "sample": "the unmodified reference on this very system in the BUILD container (8 cores, 592.7 s, "
+                                   "recorded as ref_seconds in tests/golden_big/water500_PM3_sp2_c2.npz); too long to "
+                                   "repeat inside a bench run"}})
 
 
-def run_organics(args, rank, world, local_rank):
+def run_organics(ctx):
     """Fourth workload (BASELINE.json configs[3]): MNDO SCF + forces over 65,536 mixed organics of 5-30 atoms (library of
     2048 grown molecules x 32 perturbed copies), eigh density.  STRONG scaling: the batch is cut into contiguous molecule
     ranges, one per rank (pyseqm_b200.distributed.shard_batch); every rank runs its shard as a size-bucketed sweep
     (pyseqm_b200.batching.BucketedBatch); one all_gather of the energies ends the step.  One step = the whole sweep."""
-    import ctypes
     from pyseqm_b200 import _lib, synth
     from pyseqm_b200.basics import Force
     from pyseqm_b200.batching import BucketedBatch
     from pyseqm_b200.distributed import gather_molecules, shard_bounds
     from pyseqm_b200.seqm_functions.constants import Constants
     ntotal = int(os.environ.get('SEQM_BENCH_ORGANICS', '65536'))
-    dev = torch.device('cuda', local_rank)
-    torch.cuda.set_device(dev)
+    args, rank, world, dev, local_rank = ctx.args, ctx.rank, ctx.world, ctx.dev, ctx.local_rank
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
+    nsteps = max(1, min(args.steps, int(os.environ.get('SEQM_BENCH_ORGANICS_STEPS', '3'))))
     par = dict(method='MNDO', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6, 7, 8], learned=[],
                pair_outer_cutoff=1.0e10)
     sp, xyz = synth.mixed_organics_sweep(ntotal, seed=0)
@@ -656,15 +765,11 @@ def run_organics(args, rank, world, local_rank):
             gather_molecules(Etot, ntotal, world)
         return f, Etot, nc
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    barrier = ctx.barrier
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    for _ in range(args.warmup):
+    for _ in range(min(args.warmup, 2)):
         f, Etot, nc = step(coords)
     nfail = int(nc.sum())
     barrier()
@@ -672,7 +777,7 @@ def run_organics(args, rank, world, local_rank):
     l0 = L.seqm_launch_count()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for _ in range(args.steps):
+    for _ in range(nsteps):
         step(coords)
     b.record()
     barrier()
@@ -682,7 +787,7 @@ def run_organics(args, rank, world, local_rank):
     e_host = torch.empty(nloc).pin_memory()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(nsteps):
         f, Etot, nc = step(coords_host.to(dev, non_blocking=True))
         f_host.copy_(f, non_blocking=True)
         e_host.copy_(Etot, non_blocking=True)
@@ -699,22 +804,11 @@ def run_organics(args, rank, world, local_rank):
         t[2] = nf[0]
     total_ms, e2e_ms, nfail = float(t[0]), float(t[1]), int(t[2])
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
     L.seqm_profile_enable(1)
     bb.run(fm, const, coords)
     torch.cuda.synchronize()
-    buf = ctypes.create_string_buffer(1 << 16)
-    L.seqm_profile_report(buf, len(buf))
-    L.seqm_profile_enable(0)
-    prof = {}
-    for line in buf.value.decode().splitlines():
-        nm, ms, cnt = line.rsplit(' ', 2)
-        prof[nm] = {"ms": float(ms), "launch_groups": int(cnt)}
-    tot_prof = sum(v["ms"] for v in prof.values()) or 1.0
-    for v in prof.values():
-        v["share"] = v["ms"] / tot_prof
+    prof, tot_prof = profile_report(L)
     top = max(prof, key=lambda k: prof[k]["ms"])
     hbm, peak_src = peaks()
     # integrals + matrices each SCF kernel must move at least once, summed over the buckets
@@ -730,18 +824,14 @@ def run_organics(args, rank, world, local_rank):
             "note": "algorithmic bytes of the whole sweep (integrals once + 4 packed matrices per molecule) over the sum of "
                     "the profiled kernel times of one sweep; the SCF kernels are latency / FP64-issue bound (DESIGN.md), "
                     "one-launch warp SCF %.1f ms of %.1f ms" % (small_ms, tot_prof)}
-    sys.path.insert(0, os.path.join(ROOT, 'oracle'))
-    import seqm_oracle as orc
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    cpu = CpuPath()
+    cores = cpu.cores
     ns = 512
-    t0 = time.time()
-    orc.run(torch.as_tensor(sp[:ns]), torch.as_tensor(xyz[:ns]), method='MNDO', scf_eps=1e-6, converger=(2, 0.0))
-    cpu_s = time.time() - t0
-    ms_step = total_ms / args.steps
-    print(json.dumps({
+    cpu_s = cpu.force_seconds(sp[:ns], xyz[:ns], 'MNDO')
+    ms_step = total_ms / nsteps
+    return ({
         "metric": "SCF molecules/sec", "value": ntotal / (ms_step * 1e-3), "unit": "molecules/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "steps": nsteps, "warmup": min(args.warmup, 2), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": "MNDO SCF+forces sweep, %d mixed organics of 5-30 atoms (2048 grown molecules x perturbed "
                                "copies), eigh, converger [2], scf_eps 1e-6, sharded by molecule over %d GPU(s) "
@@ -749,13 +839,11 @@ def run_organics(args, rank, world, local_rank):
                    "molecules_per_gpu": nloc, "buckets_rank0": bb.summary(), "concurrent_bucket_workers": workers,
                    "l2": "working set of a sweep (integrals + matrices of %d molecules) exceeds L2" % nloc,
                    "scf_not_converged": nfail},
-        "e2e": {"value": ntotal / (e2e_ms / args.steps * 1e-3), "unit": "molecules/s",
+        "e2e": {"value": ntotal / (e2e_ms / nsteps * 1e-3), "unit": "molecules/s",
                 "h2d_bytes_per_step": nloc * 30 * 3 * 8, "d2h_bytes_per_step": nloc * 30 * 3 * 8 + nloc * 8},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
-        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": "port",
-                         "sample": "the first %d molecules of the sweep, one Force-equivalent call of the oracle" % ns}}))
-    if world > 1:
-        dist.destroy_process_group()
+        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": cpu.kind,
+                         "sample": "the first %d molecules of the sweep, one Force call" % ns}})
 
 
 def main():
@@ -764,21 +852,45 @@ def main():
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200')
-    ap.add_argument('--workload', default='benzene', choices=['benzene', 'c60xl', 'water', 'organics'])
+    ap.add_argument('--workload', default='all', choices=['all', 'benzene', 'c60xl', 'water', 'organics'])
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     if args.impl == 'reference':
         run_reference(args, rank, world)
-    elif args.workload == 'c60xl':
-        run_c60xl(args, rank, world, local_rank)
-    elif args.workload == 'water':
-        run_water(args, rank, world, local_rank)
-    elif args.workload == 'organics':
-        run_organics(args, rank, world, local_rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (pyseqm_b200 has no CPU path; --impl reference times the CPU reference)")
+    ctx = Ctx(args, rank, world, local_rank)
+    torch.cuda.set_device(ctx.dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=ctx.dev)
+    runners = {'benzene': run_gpu, 'c60xl': run_c60xl, 'water': run_water, 'organics': run_organics}
+    if args.workload != 'all':
+        line = runners[args.workload](ctx)
     else:
-        run_gpu(args, rank, world, local_rank)
+        # ONE line: the headline metric (SCF molecules/s, configs[1]) at top level, the XL-BOMD half of the metric
+        # (configs[2]) under "xlbomd"; with more than one GPU also the strong-scaling sweep (configs[3]) and the
+        # single large system with the SP2 tiles sharded over the ranks (configs[4]), so that a scaling run exercises
+        # every multi-GPU form.  SEQM_BENCH_SUB=0 keeps only the headline; =all adds organics and water at N = 1 too.
+        sub = os.environ.get('SEQM_BENCH_SUB', 'auto')
+        line = run_gpu(ctx)
+        extra = {}
+        if sub != '0':
+            extra['xlbomd'] = run_c60xl(ctx)
+            if world > 1 or sub == 'all':
+                extra['organics'] = run_organics(ctx)
+                extra['water'] = run_water(ctx)
+        if line is not None:
+            line.update({k: v for k, v in extra.items() if v is not None})
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0 and line is not None:
+        print(json.dumps(line))
 
 
 if __name__ == '__main__':

@@ -165,6 +165,7 @@ size_t seqm_sp2_workspace(int64_t nmol, int64_t molsize);
 int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                      const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active,
                      double* D, int32_t* niter, void* work, void* stream);
+unsigned long long seqm_sp2_step_count(void); /* purification steps enqueued since load (bench.py: time per step) */
 int seqm_sp2_density_async(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                            const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
                            int32_t* niter, void* work, int steps, int32_t* unfinished, void* stream);

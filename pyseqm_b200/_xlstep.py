@@ -75,6 +75,7 @@ class XLStep:
         self.graph = None
         self.want_graph = bool(graph)
         self.nsteps = 0
+        self.launches_per_step = 0
         self._event = None
 
     # ---- the launches of one step, on the current stream
@@ -150,8 +151,10 @@ class XLStep:
             if self.graph is None:
                 torch.cuda.synchronize()
                 g = torch.cuda.CUDAGraph()
+                l0 = lib().seqm_launch_count()
                 with torch.cuda.graph(g):          # capturing does not execute: the state advances only in replay()
                     self._enqueue()
+                self.launches_per_step = int(lib().seqm_launch_count() - l0)      # kernels one replay launches
                 self.graph = g
             self.graph.replay()
         else:

@@ -685,6 +685,7 @@ static bool sp2_p2p_ready(SeqmComm* cm, size_t doubles) {
 // first read comes after as many steps as the previous call needed (g_sp2_hint), so a steady-state call (MD, SCF)
 // synchronises once.
 static std::atomic<int> g_sp2_hint{2};
+static std::atomic<unsigned long long> g_sp2_steps{0};      // purification steps enqueued since load (seqm_sp2_step_count)
 constexpr int SP2_NCOUNT = 64;      // per-step live counters kept on the device (256 bytes of the workspace)
 static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int mmax, const double* F,
                    const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
@@ -813,6 +814,7 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
   // Steps are enqueued in batches; step `it` counts the molecules it leaves live in nlive[it % SP2_NCOUNT] and is a
   // no-op for finished molecules (their CTAs exit on the live flag), so running past convergence is harmless.
   auto enqueue = [&](int it) {
+    ++g_sp2_steps;
     int* counter = nlive + (it % SP2_NCOUNT);
     if (p2p) { p2p_step(it, counter); return; }
     if (sharded) { sharded_step(it, counter); return; }
@@ -874,6 +876,8 @@ int seqm_sp2_density(int64_t nmol, int64_t molsize, int mmax, const double* F, c
                      int32_t* niter, void* work, void* stream) {
   return sp2_run(nullptr, 0, nmol, molsize, mmax, F, nheavy, nhydro, nocc, eps, active, D, niter, work, stream);
 }
+
+unsigned long long seqm_sp2_step_count(void) { return g_sp2_steps.load(); }
 
 int seqm_sp2_density_async(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                            const int32_t* nhydro, const int32_t* nocc, double eps, const uint8_t* active, double* D,
