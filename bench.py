@@ -24,10 +24,22 @@ import sys
 import threading
 import time
 
+# torchrun exports OMP_NUM_THREADS=1; the CPU baseline legs (rank 0) must use the host cores the line reports
+if os.environ.get('OMP_NUM_THREADS') == '1' and int(os.environ.get('RANK', '0')) == 0:
+    os.environ['OMP_NUM_THREADS'] = str(os.cpu_count() or 1)
+
 import numpy as np
 import torch
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+T_START = time.time()
+
+
+def log(msg):
+    """progress on stderr (the JSON line is the only thing on stdout)"""
+    if int(os.environ.get('RANK', '0')) == 0:
+        sys.stderr.write("[bench %7.1fs] %s\n" % (time.time() - T_START, msg))
+        sys.stderr.flush()
 sys.path.insert(0, ROOT)
 torch.set_default_dtype(torch.float64)
 
@@ -447,6 +459,7 @@ def run_gpu(ctx):
                                 "mostly idle, stalls short_scoreboard / wait / long_scoreboard - DESIGN.md section 6)",
                      "algorithmic_tflops": flops / (kernels[top]["ms_per_launch"] * 1e-3) / 1e12,
                      "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
+    log("benzene: cpu baseline")
     # ---- CPU baseline: the reference's CPU path (oracle/_ref, else the oracle port) on this rank's batch ----
     cpu = CpuPath()
     ns, reps = NMOL, 2
@@ -586,6 +599,7 @@ def run_c60xl(ctx):
             kernels[nm_] = {"ms_per_launch": ms_, "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / (ms_ * 1e-3) / 1e9,
                             "frac_of_hbm": nbytes / (ms_ * 1e-3) / 1e9 / hbm}
     ms_step = total_ms / args.steps
+    log("xlbomd: cpu baseline")
     cpu = CpuPath()
     spc, xyzc = synth.c60(2, seed=0)
     xl_s = cpu.xlbomd_seconds_per_step(spc, xyzc, 3)
@@ -749,6 +763,7 @@ def run_organics(ctx):
     par = dict(method='MNDO', scf_eps=1.0e-6, scf_converger=[2, 0.0], sp2=[False], elements=[0, 1, 6, 7, 8], learned=[],
                pair_outer_cutoff=1.0e10)
     sp, xyz = synth.mixed_organics_sweep(ntotal, seed=0)
+    log("organics: %d molecules generated" % ntotal)
     lo, hi = shard_bounds(ntotal, world)[rank]
     species = torch.as_tensor(sp[lo:hi]).to(dev)
     coords_host = torch.as_tensor(xyz[lo:hi]).pin_memory()
@@ -757,6 +772,7 @@ def run_organics(ctx):
     const = Constants().to(dev)
     fm = Force(par).to(dev)
     bb = BucketedBatch(species)
+    log("organics: buckets built")
     workers = int(os.environ.get('SEQM_SWEEP_WORKERS', '6'))      # buckets run concurrently (threads + streams); 0: one after the other
 
     def step(x):
@@ -824,6 +840,7 @@ def run_organics(ctx):
             "note": "algorithmic bytes of the whole sweep (integrals once + 4 packed matrices per molecule) over the sum of "
                     "the profiled kernel times of one sweep; the SCF kernels are latency / FP64-issue bound (DESIGN.md), "
                     "one-launch warp SCF %.1f ms of %.1f ms" % (small_ms, tot_prof)}
+    log("organics: cpu baseline")
     cpu = CpuPath()
     cores = cpu.cores
     ns = 512
@@ -876,13 +893,18 @@ def main():
         # single large system with the SP2 tiles sharded over the ranks (configs[4]), so that a scaling run exercises
         # every multi-GPU form.  SEQM_BENCH_SUB=0 keeps only the headline; =all adds organics and water at N = 1 too.
         sub = os.environ.get('SEQM_BENCH_SUB', 'auto')
+        log("benzene")
         line = run_gpu(ctx)
         extra = {}
         if sub != '0':
+            log("xlbomd")
             extra['xlbomd'] = run_c60xl(ctx)
             if world > 1 or sub == 'all':
+                log("organics")
                 extra['organics'] = run_organics(ctx)
+                log("water")
                 extra['water'] = run_water(ctx)
+        log("done")
         if line is not None:
             line.update({k: v for k, v in extra.items() if v is not None})
     if world > 1:

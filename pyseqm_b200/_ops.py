@@ -216,6 +216,8 @@ def scf(topo, w, M, par5, P0, eps, converger, sp2, max_iter, debug, pv, status=N
     opt.debug = 1 if debug else 0
     if opt.converger not in (0, 1, 2):
         raise ValueError("scf_converger should be [0, alpha], [1] or [2]")
+    from .seqm_functions.diag import apply_check_degeneracy
+    apply_check_degeneracy(topo.mmax, sp2=bool(sp2[0]))
     use_async = status is not None and scf_is_fused(topo, sp2, debug)
     opt.async_status = 1 if use_async else 0
     P = _f64(P0).clone()

@@ -28,6 +28,9 @@ namespace seqm {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int WARP_MAX_SWEEPS = 40;
 constexpr int WV_LD = 32;              // row stride of the eigenvector store kept between SCF iterations
+// diag.CHECK_DEGENERACY of the reference (a module-level switch there, a process-wide one here:
+// seqm_eigh_check_degeneracy): orbitals degenerate with the HOMO share the remaining electrons equally
+extern int g_check_degeneracy;      // host copy, handed to the kernels as an argument
 
 __device__ __forceinline__ int pk2pd(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
 
@@ -207,7 +210,8 @@ template <int N>
 __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double* __restrict__ S1,
                                                  double* __restrict__ CS, const unsigned short* __restrict__ TAB,
                                                  double* __restrict__ Vg, int warm, double tol, int m, int no,
-                                                 int n4, double* __restrict__ e_out, double* __restrict__ v_out) {
+                                                 int n4, double* __restrict__ e_out, double* __restrict__ v_out,
+                                                 int check_degeneracy = 0) {
   constexpr int LD = WarpLd<N>::value;
   const int lane = threadIdx.x & 31;
   const bool on = lane < N;
@@ -339,6 +343,30 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     if (!((dummy >> p) & 1u) && (ep < e || (ep == e && p < lane))) ++rank;
   }
   const unsigned occmask = __ballot_sync(FULL, real && rank < no);
+  // CHECK_DEGENERACY (diag.py:79-98, construct_P): if orbitals beyond the HOMO lie within 1e-14 of it, every orbital of
+  // that degenerate set [indx1, indx2) gets the occupation (nocc - indx1) / (indx2 - indx1), the ones below it 1
+  double wocc = (real && rank < no) ? 1.0 : 0.0;
+  bool smeared = false;
+  if (check_degeneracy && no > 0 && no <= m) {
+    double ehomo = 0.0;
+#pragma unroll
+    for (int p = 0; p < N; ++p) {
+      const double ep = __shfl_sync(FULL, e, p);
+      const int rp = __shfl_sync(FULL, rank, p);
+      if (!((dummy >> p) & 1u) && rp == no - 1) ehomo = ep;
+    }
+    const bool cond = real && fabs(e - ehomo) <= 1.0e-14;
+    if (__any_sync(FULL, cond && rank >= no)) {
+      int lo = cond ? rank : 0x7fffffff, hi = cond ? rank + 1 : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        lo = min(lo, __shfl_xor_sync(FULL, lo, o));
+        hi = max(hi, __shfl_xor_sync(FULL, hi, o));
+      }
+      wocc = !real ? 0.0 : (rank < lo ? 1.0 : (rank < hi ? (double)(no - lo) / (double)(hi - lo) : 0.0));
+      smeared = true;
+    }
+  }
   if (e_out) {
     if (real) e_out[rank] = e;
     for (int i = m + lane; i < n4; i += 32) e_out[i] = 0.0;
@@ -352,8 +380,14 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
   }
   // P = 2 W W^T with W = occupied columns of V
   __syncwarp();
+  if (smeared) {      // P = 2 sum_k w_k c_k c_k^T: columns scaled by sqrt(w_k)
+    const double sq = sqrt(wocc);
 #pragma unroll
-  for (int j = 0; j < N; ++j) v[j] = ((occmask >> j) & 1u) ? v[j] : 0.0;
+    for (int j = 0; j < N; ++j) v[j] *= __shfl_sync(FULL, sq, j);
+  } else {
+#pragma unroll
+    for (int j = 0; j < N; ++j) v[j] = ((occmask >> j) & 1u) ? v[j] : 0.0;
+  }
   if (on) {
 #pragma unroll
     for (int jj = 0; jj < N / 2; ++jj)

@@ -4,13 +4,15 @@
 
 namespace seqm {
 
+int g_check_degeneracy = 0;
+
 template <int N>
 __global__ void __launch_bounds__(32)
 eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                  const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
                  const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
                  double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm,
-                 double tol) {
+                 double tol, int check_degeneracy) {
   constexpr int LD = WarpLd<N>::value;
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
@@ -39,7 +41,8 @@ eigh_warp_kernel(int S, const double* __restrict__ F, const int32_t* __restrict_
   __syncwarp();
   double* Vg = Vstore ? Vstore + (size_t)mol * WV_LD * WV_LD : nullptr;
   const int sweeps = warp_eigh_density<N>(S0, S1, CS, TAB, Vg, warm, tol, m, nocc[mol], n4,
-                                          e_out ? e_out + (size_t)mol * n4 : nullptr, v_out ? v_out + base : nullptr);
+                                          e_out ? e_out + (size_t)mol * n4 : nullptr, v_out ? v_out + base : nullptr,
+                                          check_degeneracy);
   if (info && lane == 0) info[mol] = sweeps;
   for (int i2 = 0; i2 < m; ++i2)
     if (lane < m) P[base + (size_t)pk2pd(i2, nh4) * n4 + pk2pd(lane, nh4)] = S1[i2 * LD + lane];
@@ -56,7 +59,7 @@ static int launch_n(int64_t nmol, int S, const double* F, const int32_t* nheavy,
     configured = true;
   }
   eigh_warp_kernel<N><<<(unsigned)nmol, 32, 0, st>>>(S, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore,
-                                                   warm, tol);
+                                                   warm, tol, g_check_degeneracy);
   SEQM_CHECK_LAUNCH("eigh_warp_kernel");
   return SEQM_OK;
 }
@@ -81,3 +84,8 @@ int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, con
 }
 
 }  // namespace seqm
+
+extern "C" void seqm_eigh_check_degeneracy(int on) {
+  seqm::g_check_degeneracy = on ? 1 : 0;
+}
+extern "C" int seqm_eigh_check_degeneracy_max_m(void) { return 32; }

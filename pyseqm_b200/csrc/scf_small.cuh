@@ -23,7 +23,7 @@ struct SmallScfArgs {
   double *pairvec, *Pold, *Hpk, *FOCK, *FPPF, *EMAT, *Vstore;   // Hpk: packed core Hamiltonian scratch [B][nn]
   unsigned long long* stat;      // [0] molecules left unconverged, [1] largest iteration count
   size_t nn;                     // doubles per molecule in Pold / one ring slot
-  int converger, max_iter;
+  int converger, max_iter, check_degeneracy;
   double alpha, eps, tol;
 };
 

@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     else mode = SMIX_TAKE;
     if (A.converger == 2 && k >= 5) pulay_extrapolate(counter, cF);
     SEQM_PHASE(6);
-    warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr);
+    warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr, A.check_degeneracy);
     mix(mode);
     SEQM_PHASE(10);
   }
@@ -423,7 +423,7 @@ int launch_scf_small(const seqm_topology_t& t, seqm_w_t w, const double* M, cons
   a.nheavy = nheavy; a.nhydro = nhydro; a.nocc = nocc; a.mol_atom0 = mol_atom0;
   a.P = P; a.F = F; a.E = E; a.nc = nc; a.niter = niter; a.pairvec = pairvec; a.Pold = Pold; a.Hpk = Hpk; a.FOCK = FOCK;
   a.FPPF = FPPF; a.EMAT = EMAT; a.Vstore = Vstore; a.stat = stat; a.nn = nn; a.converger = converger;
-  a.max_iter = max_iter; a.alpha = alpha; a.eps = eps; a.tol = tol;
+  a.max_iter = max_iter; a.alpha = alpha; a.eps = eps; a.tol = tol; a.check_degeneracy = g_check_degeneracy;
   int rc;
 #define SEQM_SMALL_CASE(NN) if (mp <= NN) { rc = launch_small_n<NN>(t.nmol, a, st); prof_mark("end", st); return rc; }
   SEQM_SMALL_CASE(8)

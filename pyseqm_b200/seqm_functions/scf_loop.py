@@ -12,14 +12,24 @@ RAISE_ERROR_IF_SCF_FORWARD_FAILS = False
 
 def _charges(v, nHeavy, nHydro, nmol, molsize):
     """orbital populations per atom (scf_loop.py:788-800), from the packed eigenvectors"""
-    charge = torch.zeros(nmol, molsize * 4, molsize, device=v.device, dtype=v.dtype)
-    v2 = v ** 2
-    norb = 4 * nHeavy + nHydro
-    for i in range(nmol):
-        no, nX, nH = int(norb[i]), int(nHeavy[i]), int(nHydro[i])
-        charge[i, :no, :nX] = v2[i][:no, :(4 * nX)].reshape(no, 4, nX).sum(dim=1)
-        charge[i, :no, nX:(nX + nH)] = v2[i][:no, (4 * nX):(4 * nX + nH)]
-    return charge
+    # literal index arithmetic of the reference, for all molecules at once (no host loop, no synchronisation):
+    # charge[b, r, a] = sum_c v2[b, r, c nX + a] (a < nX: the reshape(norb, 4, nX).sum(1)), = v2[b, r, 4 nX + a - nX] for
+    # the hydrogens, rows r < norb
+    dev = v.device
+    n = 4 * molsize
+    mm = v.shape[-1]
+    v2 = torch.zeros(nmol, n, n, device=dev, dtype=v.dtype)
+    v2[:, :mm, :mm] = v ** 2
+    a = torch.arange(molsize, device=dev).view(1, molsize, 1)
+    c = torch.arange(4, device=dev).view(1, 1, 4)
+    nX, nH = nHeavy.view(-1, 1, 1).long(), nHydro.view(-1, 1, 1).long()
+    heavy, hyd = a < nX, (a >= nX) & (a < nX + nH)
+    col = torch.where(heavy, c * nX + a, (4 * nX + a - nX).expand(-1, -1, 4)).clamp(0, n - 1)
+    wgt = (heavy | (hyd & (c == 0))).to(v.dtype)
+    idx = col.reshape(nmol, 1, 4 * molsize).expand(nmol, n, 4 * molsize)
+    g = torch.gather(v2, 2, idx).reshape(nmol, n, molsize, 4) * wgt.unsqueeze(1)
+    rows = (torch.arange(n, device=dev).view(1, n, 1) < (4 * nX + nH).view(-1, 1, 1)).to(v.dtype)
+    return g.sum(dim=3) * rows
 
 
 def scf_loop(const, molsize, nHeavy, nHydro, nOccMO, maskd, mask, atom_molid, pair_molid, idxi, idxj, ni, nj, xij,
