@@ -103,6 +103,21 @@ int seqm_pair_geometry(const seqm_topology_t* topo, const double* R, double lcf,
 int seqm_pair_geometry_grad(const seqm_topology_t* topo, const double* xij, const double* rij, const double* gx,
                             const double* gr, double lcf, double* gR, void* stream);
 
+/* Parser.forward (reference basics.py:43-118) on the device, with the outer cutoff: the pair list in the reference's
+ * order (molecule, a, b > a), its int64 index tensors and geometry, and the tables of seqm_topology_t, from one pass
+ * over the atom slots.  species[B][S] int64, R[B][S][3] in Angstrom.
+ *   seqm_parser_count  counts5[5][B*S] (int32): first-atom pairs of class HH / XH / XX, second-atom pairs, real-atom flag
+ *   (the caller scans the five rows exclusively into int64 offsets: off_pair = scan of the class total)
+ *   seqm_parser_fill   writes everything at those offsets; pairid_scratch: B*S*S int32 */
+int seqm_parser_count(int64_t nmol, int64_t molsize, const int64_t* species, const double* R, double cutoff,
+                      double lcf, int32_t* counts5, void* stream);
+int seqm_parser_fill(int64_t nmol, int64_t molsize, const int64_t* species, const double* R, double cutoff, double lcf,
+                     const int64_t* off_pair, const int64_t* off_hh, const int64_t* off_xh, const int64_t* off_xx,
+                     const int64_t* off_second, const int64_t* off_real, int64_t* mask, int64_t* pair_molid,
+                     int64_t* ni, int64_t* nj, int64_t* idxi64, int64_t* idxj64, double* xij, double* rij,
+                     int32_t* idxi, int32_t* idxj, int32_t* pair_cls, int32_t* pair_slot, int32_t* cls_hh,
+                     int32_t* cls_xh, int32_t* cls_xx, int32_t* perm_j, int32_t* pairid_scratch, void* stream);
+
 /* hcore() (reference hcore.py:6-167) = two-centre integrals + rotate + diatomic overlap + core
  * Hamiltonian, and pair_nuclear_energy() (energy.py:38-78).
  *   xij[P][3], rij[P]      Parser geometry (unit vector i->j, distance in bohr)

@@ -47,8 +47,9 @@ class EnergyXL(torch.nn.Module):
                 parameters = self.packpar(Z, learned_params=learned_parameters(species, coordinates))
             else:
                 parameters = self.packpar(Z, learned_params=learned_parameters)
+            lt = self.parser.last_topology
             st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
-                               self.method, run_scf=False)
+                               self.method, run_scf=False, topo=lt[1] if (lt is not None and lt[0] is idxi) else None)
         topo = st['topo']
         sp2 = self.seqm_parameters['sp2']
         with torch.no_grad():

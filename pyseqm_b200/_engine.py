@@ -166,8 +166,12 @@ class Prepared:
         self.key = (species.data_ptr(), species._version, tuple(species.shape), str(species.device), method,
                     _token(packpar))
         self.parameters = packpar(self.Z, learned_params=dict())
-        self.topo = PairTopology(self.nmol, self.molsize, self.Z, self.maskd, self.idxi, self.idxj, self.nHeavy,
-                                 self.nHydro, self.nocc)
+        lt = getattr(parser, 'last_topology', None)
+        if lt is not None and lt[0] is self.idxi:          # tables already built on the device by the Parser kernels
+            self.topo = lt[1]
+        else:
+            self.topo = PairTopology(self.nmol, self.molsize, self.Z, self.maskd, self.idxi, self.idxj, self.nHeavy,
+                                     self.nHydro, self.nocc)
         self.atompar = _ops.atom_pack(self.topo, self.parameters, method)
         self.P_guess = initial_density(const, self.topo, self.Z, self.maskd)
         p = self.parameters

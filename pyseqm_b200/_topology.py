@@ -70,6 +70,37 @@ class PairTopology:
         self.c = t
         self.device = dev
 
+    @classmethod
+    def from_device(cls, nmol, molsize, natoms, npairs, Z, atom_mol, atom_slot, idxi, idxj, pair_cls, pair_slot,
+                    cls_pairs, ncls, start_i, start_j, perm_j, nHeavy, nHydro, nocc, mmax, uniform):
+        """topology whose tables were produced on the device by the Parser kernels (_parser.device_parse): int32 tensors
+        taken as they are, no index arithmetic and no synchronisation here"""
+        self = cls.__new__(cls)
+        i32 = torch.int32
+        self.nmol, self.molsize, self.natoms, self.npairs = int(nmol), int(molsize), int(natoms), int(npairs)
+        self.Z, self.atom_mol, self.atom_slot, self.idxi, self.idxj = Z, atom_mol, atom_slot, idxi, idxj
+        self.pair_cls, self.pair_slot, self.cls_pairs, self.ncls = pair_cls, pair_slot, list(cls_pairs), [int(k) for k in ncls]
+        self.start_i, self.start_j, self.perm_j = start_i, start_j, perm_j
+        self.nheavy = nHeavy.to(i32).contiguous()
+        self.nhydro = nHydro.to(i32).contiguous()
+        self.nocc = nocc.to(i32).contiguous()
+        self.mmax, self.uniform = int(mmax), bool(uniform)
+        self.device = Z.device
+        self._fill_struct()
+        return self
+
+    def _fill_struct(self):
+        t = Topology()
+        t.nmol, t.molsize, t.natoms, t.npairs = self.nmol, self.molsize, self.natoms, self.npairs
+        t.Z, t.atom_mol, t.atom_slot = self.Z.data_ptr(), self.atom_mol.data_ptr(), self.atom_slot.data_ptr()
+        t.idxi, t.idxj = self.idxi.data_ptr(), self.idxj.data_ptr()
+        t.pair_cls, t.pair_slot = self.pair_cls.data_ptr(), self.pair_slot.data_ptr()
+        for c in range(3):
+            t.cls_pairs[c] = self.cls_pairs[c].data_ptr()
+            t.ncls[c] = self.ncls[c]
+        t.start_i, t.start_j, t.perm_j = self.start_i.data_ptr(), self.start_j.data_ptr(), self.perm_j.data_ptr()
+        self.c = t
+
     def ref(self):
         return ctypes.byref(self.c)
 

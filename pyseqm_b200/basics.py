@@ -32,8 +32,19 @@ class Parser(torch.nn.Module):
         super().__init__()
         self.outercutoff = seqm_parameters['pair_outer_cutoff']
         self.elements = seqm_parameters['elements']
+        # pyseqm_b200 extension: 'parser': 'torch' keeps the index arithmetic below on CUDA tensors too (comparison /
+        # test hook); the default on CUDA float64 inputs is the device kernel pair of _parser.device_parse
+        self.backend = seqm_parameters.get('parser', 'device')
+        self.last_topology = None
 
     def forward(self, constansts, species, coordinates, *args, **kwargs):
+        self.last_topology = None
+        if (self.backend == 'device' and coordinates.is_cuda and coordinates.dtype == torch.float64
+                and species.dtype == torch.int64 and not args):
+            from ._parser import device_parse
+            out, topo = device_parse(constansts, species, coordinates, self.outercutoff, kwargs.get('charges'))
+            self.last_topology = (out[12], topo)          # keyed by the idxi tensor it belongs to
+            return out
         device = coordinates.device
         nmol, molsize = species.shape
         nonblank = species > 0
@@ -182,10 +193,12 @@ class Energy(torch.nn.Module):
                 if torch.is_tensor(v) and v.requires_grad:
                     raise NotImplementedError("gradients with respect to parameter '%s' are outside the B200 hot path"
                                               % k)
+            lt = self.parser.last_topology
             st = _engine.build(const, nmol, molsize, nHeavy, nHydro, nocc, Z, maskd, idxi, idxj, xij, rij, parameters,
                                self.method, run_scf=True, P0=P0, eps=H.eps_host(), sp2=H.sp2,
                                scf_converger=H.scf_converger, max_iter=_scf_loop_mod.MAX_ITER,
-                               debug=_scf_loop_mod.debug, defer_status=self._defer_status)
+                               debug=_scf_loop_mod.debug, defer_status=self._defer_status,
+                               topo=lt[1] if (lt is not None and lt[0] is idxi) else None)
         P, notconverged = st['P'], st['notconverged']
         Eelec, EnucAB = _ops.PairEnergy.apply(xij, rij, st)
         e = charge = None

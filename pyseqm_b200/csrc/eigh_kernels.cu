@@ -108,7 +108,10 @@ eigh_density_kernel(int S, int ldmax, const double* __restrict__ F, const int32_
     }
     off = block_sum(off, red);
     tot = block_sum(tot, red);
-    if (off == 0.0 || last) break;
+    // done: exactly diagonal, the announced last sweep has run, or the residual is already at the level a last sweep
+    // would be run for anyway (off^2 <= tol^1.5 tot^2, i.e. 1e-12 of the norm at the default tol: quadratic convergence
+    // often jumps from 1e-6 straight there, and one more sweep would only polish rounding noise)
+    if (off == 0.0 || last || off <= tol * sqrt(tol) * tot) break;
     if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
     for (int r = 0; r < mp - 1; ++r) {
       if (tid < half) {

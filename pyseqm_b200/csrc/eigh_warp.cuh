@@ -299,7 +299,10 @@ __device__ __forceinline__ int warp_eigh_density(double* __restrict__ S0, double
     }
     off = warp_sum(off);
     tot = warp_sum(tot);
-    if (off == 0.0 || last) break;
+    // done: exactly diagonal, the announced last sweep has run, or the residual is already at the level a last sweep
+    // would be run for anyway (off^2 <= tol^1.5 tot^2, i.e. 1e-12 of the norm at the default tol: quadratic convergence
+    // often jumps from 1e-6 straight there, and one more sweep would only polish rounding noise)
+    if (off == 0.0 || last || off <= tol * sqrt(tol) * tot) break;
     if (off <= tol * tot) last = true;      // quadratic convergence: one more sweep squares the residual
     // the schedule entries of the next two rounds are fetched while the current two run (their shared-memory
     // latency sat on the critical path of every round: ncu source view, r01p)

@@ -544,12 +544,13 @@ __global__ void pair_geometry_kernel(seqm_topology_t t, const double* __restrict
   const int S = (int)t.molsize;
   const double* ri = R + ((size_t)t.atom_mol[i] * S + t.atom_slot[i]) * 3;
   const double* rj = R + ((size_t)t.atom_mol[j] * S + t.atom_slot[j]) * 3;
-  const double dx = rj[0] - ri[0], dy = rj[1] - ri[1], dz = rj[2] - ri[2];
-  double d2 = dx * dx + dy * dy + dz * dz;
+  // the reference's arithmetic operation by operation, no FMA contraction: bit-identical to basics.py:91-108
+  const double dx = __dsub_rn(rj[0], ri[0]), dy = __dsub_rn(rj[1], ri[1]), dz = __dsub_rn(rj[2], ri[2]);
+  double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
   if (d2 == 0.0) d2 = 1.0e-4;
-  const double dist = sqrt(d2);
-  xij[3 * p] = dx / dist; xij[3 * p + 1] = dy / dist; xij[3 * p + 2] = dz / dist;
-  rij[p] = dist * lcf;
+  const double dist = __dsqrt_rn(d2);
+  xij[3 * p] = __ddiv_rn(dx, dist); xij[3 * p + 1] = __ddiv_rn(dy, dist); xij[3 * p + 2] = __ddiv_rn(dz, dist);
+  rij[p] = __dmul_rn(dist, lcf);
 }
 
 __device__ __forceinline__ void pair_geom_grad_one(const double* __restrict__ xij, const double* __restrict__ rij,
