@@ -12,6 +12,66 @@ KINETIC_ENERGY_SCALE = 1.0364270099032438e2  # amu (A/fs)^2 -> eV
 EV_TO_KELVIN = 1.160451812e4
 
 
+class Geometry_Optimization_SD_LS(torch.nn.Module):
+    """steepest descent with a per-molecule line search over five trial step lengths (0.5 ... 1.5 times the current
+    one, the lowest total energy wins; reference MolecularDynamics.py:5-87, marked "not finished" there)"""
+
+    TRIAL = (0.5, 0.75, 1.0, 1.25, 1.5)
+
+    def __init__(self, seqm_parameters, alpha=0.01, force_tol=1.0e-4, energy_tol=1.0e-4, max_evl=1000):
+        super().__init__()
+        self.seqm_parameters = seqm_parameters
+        self.alpha, self.force_tol, self.energy_tol, self.max_evl = alpha, force_tol, energy_tol, max_evl
+        self.force = Force(seqm_parameters)
+
+    def onestep(self, const, coordinates, species, alpha, learned_parameters=dict(), P0=None, *args, **kwargs):
+        force, P, L = self.force(const, coordinates, species, learned_parameters=learned_parameters, P0=P0,
+                                 *args, **kwargs)[:3]
+        P = P.detach()
+        trial = torch.tensor(self.TRIAL, dtype=coordinates.dtype, device=coordinates.device)
+        alphas = alpha.unsqueeze(1) * trial.reshape(1, -1)
+        with torch.no_grad():
+            eng = torch.zeros_like(alphas)
+            for k in range(alphas.shape[1]):
+                moved = (coordinates + force * alphas[:, k].reshape(-1, 1, 1)).detach()
+                eng[:, k] = self.force.energy(const, moved, species, learned_parameters=learned_parameters,
+                                              all_terms=True, P0=P0, *args, **kwargs)[1]
+            alpha = alphas.gather(1, torch.argmin(eng, dim=1, keepdim=True)).reshape(-1)
+            coordinates.add_(alpha.reshape(-1, 1, 1) * force)
+        return coordinates, force, P, L, alpha
+
+    def run(self, const, coordinates, species, learned_parameters=dict(), P=None, log=True, *args, **kwargs):
+        nmol = coordinates.shape[0]
+        coordinates.requires_grad_(True)
+        alpha = torch.full((nmol,), float(self.alpha), dtype=coordinates.dtype, device=coordinates.device)
+        Lold = torch.zeros(nmol, dtype=coordinates.dtype, device=coordinates.device)
+        force_err = energy_err = None
+        converged = False
+        for i in range(self.max_evl):
+            coordinates, force, P, Lnew, alpha = self.onestep(const, coordinates, species, alpha,
+                                                              learned_parameters=learned_parameters, P0=P, *args, **kwargs)
+            with torch.no_grad():
+                if torch.is_tensor(coordinates.grad):
+                    coordinates.grad.zero_()
+                alpha = alpha.clamp_min(1.0e-3)
+                force_err = torch.max(torch.abs(force))
+                energy_err = (Lnew - Lold).sum() / nmol
+            if log:
+                print("%d %e " % (i + 1, force_err.item()), end="")
+                print(" ".join("%e %e %e" % (a, b, a - b) for a, b in zip(Lnew.tolist(), Lold.tolist())))
+            if force_err > self.force_tol:
+                Lold = Lnew.detach().clone()
+                continue
+            converged = True
+            break
+        if not converged:
+            print('not converged within %d step' % self.max_evl)
+        elif log:
+            print("converged with %d step, Max Force = %e (eV/Ang), dE = %e (eV)" % (i + 1, force_err.item(),
+                                                                                     energy_err.item()))
+        return coordinates, force_err, energy_err
+
+
 class Geometry_Optimization_SD(torch.nn.Module):
     """steepest descent: x <- x + alpha * force until max |force| < force_tol (reference :103-157)"""
 

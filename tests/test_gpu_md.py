@@ -17,7 +17,8 @@ GMD = os.path.join(ROOT, 'tests', 'golden_md')
 
 @pytest.mark.parametrize('tag,mode', [('bomd_eigh', 'autograd'), ('xlbomd_sp2', 'fused'), ('xlbomd_sp2', 'graph'),
                                       ('xlbomd_sp2', 'autograd'), ('xlbomd_eigh', 'fused'), ('xlbomd_eigh', 'graph'),
-                                      ('xlbomd_eigh', 'autograd')])
+                                      ('xlbomd_eigh', 'autograd'), ('xlbomd_c60_sp2', 'fused'), ('xlbomd_c60_sp2', 'graph'),
+                                      ('xlbomd_c60_sp2', 'autograd')])
 def test_md_trajectory(tag, mode):
     """mode (XL-BOMD only): 'fused' = the step as a fixed sequence of library launches (_xlstep.XLStep, the default),
     'graph' = the same captured in one CUDA graph, 'autograd' = the reference-shaped form (EnergyXL + torch.autograd)"""
@@ -27,7 +28,8 @@ def test_md_trajectory(tag, mode):
     dev = torch.device('cuda:0')
     g = np.load(os.path.join(GMD, tag + '.npz'))
     sp2 = g['sp2'].tolist()
-    par = dict(method='AM1', scf_eps=1e-8, scf_converger=[2, 0.0], sp2=[bool(sp2[0])] + sp2[1:],
+    par = dict(method=str(g['method']) if 'method' in g else 'AM1', scf_eps=float(g['eps']) if 'eps' in g else 1e-8,
+               scf_converger=[2, 0.0], sp2=[bool(sp2[0])] + sp2[1:],
                elements=[0, 1, 6, 8], learned=[], pair_outer_cutoff=1e10, xl_fused=(mode != 'autograd'),
                xl_cuda_graph=(mode == 'graph'))
     out = {'molid': [0, 1], 'thermo': 1, 'dump': 10 ** 9, 'prefix': '/tmp/seqm_b200_md'}
