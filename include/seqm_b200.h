@@ -152,6 +152,22 @@ size_t seqm_elec_energy_workspace(int64_t nmol, int64_t molsize);
 int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
                      const double* D, int xl, const uint8_t* active, double* E, void* work, void* stream);
 
+/* seqm_elec_energy for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and arithmetic as the chunked form of seqm_elec_energy (per-chunk partial sums of 8192 matrix
+ * elements, added in a fixed order), but the partial sums live in a file-scope `static __device__` array of
+ * SEQM_NOALLOC_MAX_PARTIALS doubles (512 KiB, held by every GPU that loads the library until exit) instead of caller
+ * scratch: the call allocates nothing - no cudaMalloc / cudaFree, no allocating library routine - and takes no
+ * workspace argument.  Limit: nmol * ceil(16 * molsize^2 / 8192) <= SEQM_NOALLOC_MAX_PARTIALS, otherwise SEQM_EINVAL with
+ * a message that names the sizes (e.g. 65,536 molecules of up to 22 atoms, or one system of up to 5,792 atoms).
+ * The array is shared by every call on a device and keeps the last call's contents; nothing in it needs clearing (a call
+ * only reads partial sums it has written itself), but two calls that OVERLAP on the GPU (different streams) race on it:
+ * serialise them.  The first call on a device resolves the array's device address (cudaGetSymbolAddress, once per
+ * device with that device current): make that first call outside stream capture. */
+#define SEQM_NOALLOC_MAX_PARTIALS 65536
+int seqm_elec_energy_noalloc(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
+                             const double* D, int xl, const uint8_t* active, double* E, void* stream);
+
 /* sym_eig_trunc() (reference diag.py:102-172) with pack/unpack (pack.py:7-41) folded in: batched
  * symmetric eigensolver on the packed matrix (heavy atoms 4 orbitals, hydrogens 1) and
  * P = 2 C_occ C_occ^T written back in padded layout.  One CTA per molecule, cyclic Jacobi in shared

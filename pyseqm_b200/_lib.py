@@ -78,6 +78,7 @@ def lib():
         L.seqm_fock.argtypes = [TP, WStore] + [VP] * 13
         L.seqm_elec_energy.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP, VP]
         L.seqm_elec_energy_workspace.argtypes = [i64, i64]
+        L.seqm_elec_energy_noalloc.argtypes = [i64, i64, VP, VP, VP, VP, ci, VP, VP, VP]
         L.seqm_elec_energy_workspace.restype = ctypes.c_size_t
         L.seqm_eigh_density.argtypes = [i64, i64, ci] + [VP] * 10
         L.seqm_sp2_density.argtypes = [i64, i64, ci, VP, VP, VP, VP, cd, VP, VP, VP, VP, VP]
@@ -128,7 +129,7 @@ EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile
            'seqm_sp2_density', 'seqm_sp2_density_async', 'seqm_sp2_step_count', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
            'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
            'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse',
-           'seqm_eigh_check_degeneracy', 'seqm_eigh_check_degeneracy_max_m', 'seqm_parser_count', 'seqm_parser_fill', 'seqm_xl_extrapolate', 'seqm_verlet_kick_drift', 'seqm_verlet_finish', 'seqm_energy_finish', 'seqm_md_thermo']
+           'seqm_elec_energy_noalloc', 'seqm_eigh_check_degeneracy', 'seqm_eigh_check_degeneracy_max_m', 'seqm_parser_count', 'seqm_parser_fill', 'seqm_xl_extrapolate', 'seqm_verlet_kick_drift', 'seqm_verlet_finish', 'seqm_energy_finish', 'seqm_md_thermo']
 
 
 def check(rc, what):

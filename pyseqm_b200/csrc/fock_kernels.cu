@@ -6,6 +6,8 @@
 //                          vectors + core block, written to both triangles of the diagonal block
 //   elec_energy_kernel     one CTA per molecule, 0.5 sum P.(H+F)   (or the XL-BOMD shadow energy)
 // reference: seqm/seqm_functions/fock.py:6-139, energy.py:19-36, XLBOMD.py:40-52
+#include <mutex>
+
 #include "abi_common.cuh"
 #include "dgemm.cuh"
 
@@ -303,6 +305,33 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
   return SEQM_OK;
 }
 
+// ---- allocation-free variant of the chunked energy sum (seqm_elec_energy_noalloc) -----------------------------------
+// Its partial sums live in a file-scope device array instead of caller scratch: 512 KiB that every GPU loading the
+// library holds until exit.  All calls on a device share the array: calls that overlap on the GPU (different streams)
+// race on it.  Nothing in it has to start at zero - every partial sum a call reads was written by that same call.
+constexpr size_t NOALLOC_MAX_PARTIALS = SEQM_NOALLOC_MAX_PARTIALS;
+static __device__ __align__(256) double g_noalloc_part[NOALLOC_MAX_PARTIALS];
+
+// Device address of g_noalloc_part on the CURRENT device.  In host code the symbol's name is only a host-side stand-in,
+// not a device address, so it is resolved with cudaGetSymbolAddress - once per device, with that device current.
+static int noalloc_scratch(double** out) {
+  constexpr int MAXDEV = 64;
+  static std::mutex mtx;
+  static double* ptrs[MAXDEV] = {nullptr};
+  int dev = -1;
+  SEQM_CUDA(cudaGetDevice(&dev));
+  SEQM_REQUIRE(dev >= 0 && dev < MAXDEV, "seqm_elec_energy_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mtx);
+  if (!ptrs[dev]) {
+    double* p = nullptr;
+    SEQM_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_part));
+    SEQM_REQUIRE(p != nullptr, "seqm_elec_energy_noalloc: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return SEQM_OK;
+}
+
 }  // namespace seqm
 
 using namespace seqm;
@@ -323,6 +352,34 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
   SEQM_REQUIRE(!xl || D, "seqm_elec_energy: xl needs D");
   if (nmol == 0) return SEQM_OK;
   return launch_elec_energy(nmol, molsize, P, F, M, D, xl, active, E, (double*)work, (cudaStream_t)stream);
+}
+
+int seqm_elec_energy_noalloc(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
+                             const double* D, int xl, const uint8_t* active, double* E, void* stream) {
+  SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0, "seqm_elec_energy_noalloc: bad argument");
+  SEQM_REQUIRE(!xl || D, "seqm_elec_energy_noalloc: xl needs D");
+  if (nmol == 0) return SEQM_OK;
+  const size_t nn = (size_t)16 * molsize * molsize;
+  const int chunks = red_chunks(nn);
+  if ((unsigned long long)nmol * (unsigned long long)chunks > (unsigned long long)NOALLOC_MAX_PARTIALS) {
+    char msg[256];
+    snprintf(msg, sizeof msg,
+             "seqm_elec_energy_noalloc: %lld molecules x %d chunks of 8192 matrix elements = %lld partial sums exceed the "
+             "static scratch of %lld (SEQM_NOALLOC_MAX_PARTIALS); use seqm_elec_energy with caller scratch",
+             (long long)nmol, chunks, (long long)nmol * chunks, (long long)NOALLOC_MAX_PARTIALS);
+    return fail(SEQM_EINVAL, msg);
+  }
+  double* part = nullptr;
+  const int rc = noalloc_scratch(&part);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  prof_mark("elec_energy", st);
+  // always the chunked pair of kernels (also when a molecule is a single chunk): partial sums -> fixed-order sum
+  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, part);
+  SEQM_CHECK_LAUNCH("elec_energy_part_kernel");
+  const int rc2 = launch_chunk_sum((int)nmol, chunks, active, 1, part, E, nullptr, st);
+  prof_mark("end", st);
+  return rc2;
 }
 
 size_t seqm_elec_energy_workspace(int64_t nmol, int64_t molsize) {
