@@ -177,6 +177,7 @@ int seqm_elec_energy_noalloc(int64_t nmol, int64_t molsize, const double* P, con
  *   info[B] (may be NULL) sweeps used.  mmax: largest packed size in the batch (sizes shared memory). */
 int seqm_eigh_max_m(void);
 void seqm_eigh_force_block(int on); /* process-wide test hook: shared-memory (CTA) Jacobi also for m <= 32 */
+void seqm_eigh_warp_variant(int ring); /* process-wide test hook: warp kernels (m <= 32, stand-alone and inside the one-launch SCF): 1 (default) = one-sided ring Jacobi in registers (csrc/eigh_ring.cuh), 0 = two-sided odd-even Jacobi (csrc/eigh_warp.cuh) */
 void seqm_eigh_block_config(int bits); /* process-wide tuning hook: shared-memory Jacobi variants for 32 < m <= 64: bit 0 = 256-thread CTAs (4 per SM) for m <= 48, bit 1 = FP32 rotation tangent (FP64 cosine) for m <= 64; default 3 (measured 135 -> 118 ms on the m > 32 molecules of config 4, tools/exp_organics_big.py) */
 void seqm_eigh_tolerance(double tol); /* process-wide: Jacobi stopping rule, one final sweep once off^2 <= tol * total^2 (default 1e-16 for both kernels - r02a: 1e-14 fails the 1e-9 density check on one fixture, 1e-16 passes all and is 4.6 % faster than 1e-18; tol <= 0 restores it) */
 /* process-wide, like the reference's module-level diag.CHECK_DEGENERACY (diag.py:7-10,79-98): orbitals within 1e-14 of

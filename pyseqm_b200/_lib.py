@@ -57,6 +57,8 @@ def lib():
         L.seqm_eigh_force_block.argtypes = [ctypes.c_int]
         L.seqm_eigh_force_block.restype = None
         L.seqm_eigh_tolerance.argtypes = [ctypes.c_double]
+        L.seqm_eigh_warp_variant.argtypes = [ctypes.c_int]
+        L.seqm_eigh_warp_variant.restype = None
         L.seqm_eigh_check_degeneracy.argtypes = [ctypes.c_int]
         L.seqm_eigh_check_degeneracy.restype = None
         L.seqm_pair_grad_reverse.argtypes = [ctypes.c_int]
@@ -114,10 +116,12 @@ def lib():
             fn = getattr(L, name)
             if name not in ('seqm_last_error', 'seqm_atompar_bytes', 'seqm_sp2_workspace', 'seqm_scf_workspace',
                             'seqm_launch_count', 'seqm_sp2_step_count', 'seqm_eigh_check_degeneracy', 'seqm_profile_enable', 'seqm_eigh_force_block', 'seqm_eigh_tolerance', 'seqm_scf_fused',
-                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm'):
+                            'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse', 'seqm_sp2_nccl_workspace', 'seqm_scf_sp2_comm', 'seqm_eigh_warp_variant'):
                 fn.restype = ctypes.c_int
         if os.environ.get('SEQM_EIGH_CFG'):
             L.seqm_eigh_block_config(int(os.environ['SEQM_EIGH_CFG']))
+        if os.environ.get('SEQM_EIGH_WARP_VARIANT'):
+            L.seqm_eigh_warp_variant(int(os.environ['SEQM_EIGH_WARP_VARIANT']))
         if os.environ.get('SEQM_EIGH_TOL'):
             L.seqm_eigh_tolerance(float(os.environ['SEQM_EIGH_TOL']))
         _lib = L
@@ -129,7 +133,7 @@ EXPORTS = ['seqm_last_error', 'seqm_version', 'seqm_launch_count', 'seqm_profile
            'seqm_sp2_density', 'seqm_sp2_density_async', 'seqm_sp2_step_count', 'seqm_scf_workspace', 'seqm_scf_fused', 'seqm_scf', 'seqm_pair_grad', 'seqm_dgemm_batched', 'seqm_pair_geometry', 'seqm_pair_geometry_grad',
            'seqm_nccl_unique_id', 'seqm_nccl_comm_create', 'seqm_nccl_comm_destroy', 'seqm_sp2_nccl_subchunks', 'seqm_sp2_shard_plan',
            'seqm_sp2_nccl_workspace', 'seqm_sp2_density_nccl', 'seqm_scf_sp2_comm', 'seqm_elec_energy_workspace', 'seqm_sp2_nccl_p2p', 'seqm_eigh_block_config', 'seqm_pair_grad_reverse',
-           'seqm_elec_energy_noalloc', 'seqm_eigh_check_degeneracy', 'seqm_eigh_check_degeneracy_max_m', 'seqm_parser_count', 'seqm_parser_fill', 'seqm_xl_extrapolate', 'seqm_verlet_kick_drift', 'seqm_verlet_finish', 'seqm_energy_finish', 'seqm_md_thermo']
+           'seqm_elec_energy_noalloc', 'seqm_eigh_check_degeneracy', 'seqm_eigh_check_degeneracy_max_m', 'seqm_parser_count', 'seqm_parser_fill', 'seqm_xl_extrapolate', 'seqm_verlet_kick_drift', 'seqm_verlet_finish', 'seqm_energy_finish', 'seqm_md_thermo', 'seqm_eigh_warp_variant']
 
 
 def check(rc, what):

@@ -31,6 +31,7 @@ constexpr int WV_LD = 32;              // row stride of the eigenvector store ke
 // diag.CHECK_DEGENERACY of the reference (a module-level switch there, a process-wide one here:
 // seqm_eigh_check_degeneracy): orbitals degenerate with the HOMO share the remaining electrons equally
 extern int g_check_degeneracy;      // host copy, handed to the kernels as an argument
+extern int g_eigh_warp_ring;        // process-wide test hook (seqm_eigh_warp_variant): 1 = eigh_ring.cuh, 0 = this file
 
 __device__ __forceinline__ int pk2pd(int q, int nh4) { return q < nh4 ? q : nh4 + 4 * (q - nh4); }
 

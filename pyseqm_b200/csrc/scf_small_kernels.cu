@@ -19,6 +19,7 @@ __device__ long long g_phase_last;
   } while (0)
 #endif
 #include "scf_small.cuh"
+#include "eigh_ring.cuh"
 #include "dgemm.cuh"
 
 namespace seqm {
@@ -31,14 +32,14 @@ __global__ void mol_atom0_kernel(int natoms, int nmol, const int32_t* __restrict
   if (a == 0 || atom_mol[a - 1] != mol) out[mol] = a;
 }
 
-template <int N>
+template <int N, bool RING>
 __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ SmallScfArgs A) {
   constexpr int LD = WarpLd<N>::value;
   __shared__ __align__(16) double Ps[N * LD];
   __shared__ __align__(16) double S0[N * LD];
   __shared__ __align__(16) double S1[N * LD];
-  __shared__ __align__(16) double CS[3 * N];
-  __shared__ unsigned short TAB[N * 32];
+  __shared__ __align__(16) double CS[RING ? 2 : 3 * N];
+  __shared__ unsigned short TAB[RING ? 2 : N * 32];
   const seqm_topology_t& t = A.t;
   const int mol = blockIdx.x;
   const int lane = threadIdx.x;
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
 #ifdef SEQM_SCF_TIMING
   if (blockIdx.x == 0 && lane == 0) g_phase_last = clock64();
 #endif
-  build_schedule<N>(TAB, lane);
+  if constexpr (!RING) build_schedule<N>(TAB, lane);
   // ---- P0 -> packed
   for (int idx = lane; idx < N * LD; idx += 32) {
     const int i = idx / LD, j = idx - i * LD;
@@ -371,7 +372,8 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     else mode = SMIX_TAKE;
     if (A.converger == 2 && k >= 5) pulay_extrapolate(counter, cF);
     SEQM_PHASE(6);
-    warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr, A.check_degeneracy);
+    if constexpr (RING) ring_eigh_density<N>(S0, S1, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr, A.check_degeneracy);
+    else warp_eigh_density<N>(S0, S1, CS, TAB, Vg, k > 0 ? 1 : 0, A.tol, m, no, n4, nullptr, nullptr, A.check_degeneracy);
     mix(mode);
     SEQM_PHASE(10);
   }
@@ -392,17 +394,22 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   }
 }
 
-template <int N>
-static int launch_small_n(int64_t nmol, const SmallScfArgs& args, cudaStream_t st) {
+template <int N, bool RING>
+static int launch_small_nv(int64_t nmol, const SmallScfArgs& args, cudaStream_t st) {
   static thread_local bool configured = false;
   if (!configured) {
-    SEQM_CUDA(cudaFuncSetAttribute(scf_small_kernel<N>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    SEQM_CUDA(cudaFuncSetAttribute(scf_small_kernel<N, RING>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                    (int)cudaSharedmemCarveoutMaxShared));
     configured = true;
   }
-  scf_small_kernel<N><<<(unsigned)nmol, 32, 0, st>>>(args);
+  scf_small_kernel<N, RING><<<(unsigned)nmol, 32, 0, st>>>(args);
   SEQM_CHECK_LAUNCH("scf_small_kernel");
   return SEQM_OK;
+}
+
+template <int N>
+static int launch_small_n(int64_t nmol, const SmallScfArgs& args, cudaStream_t st) {
+  return g_eigh_warp_ring ? launch_small_nv<N, true>(nmol, args, st) : launch_small_nv<N, false>(nmol, args, st);
 }
 
 
