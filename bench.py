@@ -392,6 +392,7 @@ def run_gpu(ctx):
     barrier()
     launches = int(L.seqm_launch_count() - l0)
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    log("benzene: per-step ms " + " ".join("%.3f" % a.elapsed_time(b) for a, b in evs))
     # ---- end to end: pinned host coordinates in, forces + energies out, every step ----
     f_host = torch.empty(NMOL, 12, 3).pin_memory()
     e_host = torch.empty(NMOL).pin_memory()

@@ -107,8 +107,14 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
   double gp[H], gq[H];
   if (warm && Vg) {
     // V0 -> S1 (row, slot), G = (A + sigma I) V0
-    for (int r = 0; r < N; ++r)
-      if (lane < 2 * K) S1[r * LD + lane] = Vg[r * WV_LD + lane];
+    {
+      double vv[N];
+#pragma unroll
+      for (int r = 0; r < N; ++r) vv[r] = lane < 2 * K ? Vg[r * WV_LD + lane] : 0.0;
+#pragma unroll
+      for (int r = 0; r < N; ++r)
+        if (lane < 2 * K) S1[r * LD + lane] = vv[r];
+    }
     __syncwarp();
 #pragma unroll
     for (int i = 0; i < H; ++i) {
@@ -239,12 +245,14 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
     renorm();
     off = 0.0;
     const double tot = ap * ap + aq * aq;
-#pragma unroll
-    for (int Kg = K; Kg >= 1; Kg >>= 1) {      // phases, unrolled: Kg is a compile-time constant in each copy
+    // phases: ONE copy of the round in the instruction stream (the one-launch SCF kernel around this function is large
+    // and its warps run different phases: instruction-cache misses showed as no_instruction stalls when the phases
+    // were unrolled); the round that ends a phase shuffles from the own lane
+#pragma unroll 1
+    for (int Kg = K; Kg >= 1; Kg >>= 1) {
       const int src = (((k & ~(Kg - 1)) | ((k - 1) & (Kg - 1))) * R) + h;      // previous processor of the group, same row part
 #pragma unroll 1
-      for (int r = 0; r < Kg - 1; ++r) rotate(std::true_type{}, src);
-      rotate(std::false_type{}, lane);
+      for (int r = 0; r < Kg; ++r) rotate(std::true_type{}, r + 1 < Kg ? src : lane);
       if (Kg > 1) exchange(Kg >> 1);
     }
     ++sweeps;
@@ -269,6 +277,7 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
     const double ep = __shfl_sync(FULL, e, lp);
     if (((realmask >> lp) & 1u) && (ep < e || (ep == e && p < sidx))) ++rank;
   }
+  SEQM_PHASE(12);
   // CHECK_DEGENERACY (diag.py:79-98, construct_P): if orbitals beyond the HOMO lie within 1e-14 of it, every orbital of
   // that degenerate set [indx1, indx2) gets the occupation (nocc - indx1) / (indx2 - indx1), the ones below it 1
   double wocc = (real && rank < no) ? 1.0 : 0.0;
@@ -321,6 +330,7 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
     if (wQ > 0.0) S0[row * LD + rankQ] = vq * fQ;
   }
   __syncwarp();
+  SEQM_PHASE(13);
   // ---- P = 2 W W^T, lane = row
   {
     const bool on = lane < N;
@@ -332,6 +342,7 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
       w[2 * jj] = x.x;
       w[2 * jj + 1] = x.y;
     }
+#pragma unroll 2
     for (int i2 = 0; i2 < m; ++i2) {
       double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll

@@ -114,12 +114,16 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   // F(Ps) -> S0, core Hamiltonian -> S1; returns 0.5 sum P (H + F)
   auto fock = [&]() -> double {
     SEQM_PHASE(11);
-#pragma unroll 4
-    for (int i = 0; i < N; ++i) {
-      if (lane < N) {
-        const double h = Hpk[i * N + lane];
-        S1[i * LD + lane] = h;
-        S0[i * LD + lane] = h;
+    {      // all N loads of the lane in flight at once (a lone warp has nothing else to hide their latency with)
+      double hv[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) hv[i] = lane < N ? Hpk[i * N + lane] : 0.0;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        if (lane < N) {
+          S1[i * LD + lane] = hv[i];
+          S0[i * LD + lane] = hv[i];
+        }
       }
     }
     __syncwarp();
@@ -326,14 +330,22 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     double coeff[SNFOCK];
 #pragma unroll
     for (int s = 0; s < SNFOCK; ++s) coeff[s] = -x[s];
-#pragma unroll 3
-    for (int i = 0; i < N; ++i) {
-      if (lane < N) {
+    constexpr int RB = (N % 6 == 0) ? 6 : 4;      // rows per batch: RB * SNFOCK loads in flight
+#pragma unroll 1
+    for (int i0 = 0; i0 < N; i0 += RB) {
+      double fv[RB][SNFOCK];
+#pragma unroll
+      for (int ii = 0; ii < RB; ++ii)
+#pragma unroll
+        for (int s = 0; s < SNFOCK; ++s)
+          fv[ii][s] = (lane < N && s < cF && i0 + ii < N) ? FOCK[(size_t)s * A.nn + (i0 + ii) * N + lane] : 0.0;
+#pragma unroll
+      for (int ii = 0; ii < RB; ++ii) {
         double acc = 0.0;
 #pragma unroll
         for (int s = 0; s < SNFOCK; ++s)
-          if (s < cF) acc += FOCK[(size_t)s * A.nn + i * N + lane] * coeff[s];
-        S0[i * LD + lane] = acc;
+          if (s < cF) acc += fv[ii][s] * coeff[s];
+        if (lane < N && i0 + ii < N) S0[(i0 + ii) * LD + lane] = acc;
       }
     }
     __syncwarp();

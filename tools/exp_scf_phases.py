@@ -23,7 +23,7 @@ f(const, coords.clone(), species)
 L.seqm_debug_phase_ticks(buf, 1)
 names = ['setup (schedule, P0)', 'fock: core Hamiltonian init', 'fock: pairs', 'fock: atoms (diagonal blocks)', 'fock: energy',
          'pulay store', 'pulay extrapolate (+loop control)', 'eigh: load + warm-start transform', 'eigh: sweeps',
-         'eigh: store V, rank, density', 'mix', 'loop control before fock']
+         'eigh: density P = 2 W W^T', 'mix', 'loop control before fock', 'eigh: eigenvalues + ranking', 'eigh: store V / W']
 tot = sum(buf[i] for i in range(16))
 st = f.energy.last_state
 print('molecule 0: %d iterations, total %.0f kcycles' % (int(st['niter'][0]), tot / 1e3))
