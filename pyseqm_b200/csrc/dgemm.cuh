@@ -32,6 +32,10 @@ int launch_eigh_warp(int64_t nmol, int64_t molsize, int mp, const double* F, con
 
 
 int eigh_cluster_max_m();
+int launch_eigh_ring2(int64_t nmol, int64_t molsize, int mp, const double* F, const int32_t* nheavy, const int32_t* nhydro,
+                      const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out, int32_t* info,
+                      double* Vstore, int warm, double tol, cudaStream_t st);
+size_t eigh_ring2_vstore_doubles(int64_t nmol);
 int launch_eigh_cluster(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                         const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
                         double* v_out, int32_t* info, double tol, cudaStream_t st);

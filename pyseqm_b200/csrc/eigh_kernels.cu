@@ -235,6 +235,7 @@ double g_eigh_tol = 1.0e-16;      // off-diagonal^2 / total^2 at which one last 
 double g_eigh_tol_warp = 1.0e-16; // same for the warp kernel, whose ordering converges quadratically (tools/exp_eigh_tol.py)
 double eigh_tolerance() { return g_eigh_tol_warp; }
 int g_eigh_cfg = 3;      // variant hook (seqm_eigh_block_config): bit 0: 256-thread CTAs + FP32 tangent for 32 < m <= 48, bit 1: FP32 tangent for m <= 64
+extern int g_eigh_warp_ring;          // eigh_warp_kernels.cu (seqm_eigh_warp_variant)
 int g_force_block_jacobi = 0;      // test hook: use the shared-memory kernel also for m <= 32
 
 static size_t eigh_smem_bytes(int mp, bool warm) {
@@ -243,6 +244,10 @@ static size_t eigh_smem_bytes(int mp, bool warm) {
 
 size_t eigh_vstore_doubles(int64_t nmol, int mmax) {
   const int mp = (mmax + 1) & ~1;
+  if (mp > 32 && mp <= 64) {      // the two-warp ring kernel keeps [row][64 slots]; the shared-memory kernel mp x mp
+    const size_t a = eigh_ring2_vstore_doubles(nmol), b = (size_t)nmol * mp * mp;
+    return a > b ? a : b;
+  }
   return mmax <= EIGH_WARM_MAX_M ? (size_t)nmol * mp * mp : 0;
 }
 
@@ -289,6 +294,8 @@ int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F
     rc = launch_eigh_warp(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 32)
     rc = launch_cfg<256, 7, false>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
+  else if (mp <= 64 && g_eigh_warp_ring && !g_force_block_jacobi)
+    rc = launch_eigh_ring2(nmol, molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol_warp, st);
   else if (mp <= 48 && (g_eigh_cfg & 1))
     rc = launch_cfg<256, 4, true>(nmol, smem, st, (int)molsize, mp, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, g_eigh_tol);
   else if (mp <= 64 && (g_eigh_cfg & 2))

@@ -62,6 +62,114 @@ template <int R> __device__ __forceinline__ double ring_sum(double v) {
   return v;
 }
 
+// The columns P, Q of one processor as seen by one of its R lanes (H rows of each), their scales (true column =
+// d * stored column, fast Givens), their carried squared norms, and the sum of gamma^2 met in the current sweep.
+template <int H, int R> struct RingCols {
+  double gp[H], gq[H];
+  double dp, idp, dq, idq, ap, aq, off;
+
+  // fold the scales into the columns and recompute the norms exactly
+  __device__ __forceinline__ void renorm() {
+    double sp_ = 0.0, sq_ = 0.0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      gp[i] *= dp;
+      gq[i] *= dq;
+      sp_ = fma(gp[i], gp[i], sp_);
+      sq_ = fma(gq[i], gq[i], sq_);
+    }
+    ap = ring_sum<R>(sp_);
+    aq = ring_sum<R>(sq_);
+    dp = idp = dq = idq = 1.0;
+  }
+
+  // one rotation of the columns P, Q; the rotated Q column (and its scalars) then moves on: it is read from lane `from`
+  // (the own lane in the round that ends a phase)
+  __device__ __forceinline__ void rotate(int from) {
+    SEQM_TICK(0);
+    double g0 = 0.0, g1 = 0.0, g2_ = 0.0, g3 = 0.0;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      if (H > 16 && (i & 3) == 2) g2_ = fma(gp[i], gq[i], g2_);
+      else if (H > 16 && (i & 3) == 3) g3 = fma(gp[i], gq[i], g3);
+      else if (i & 1) g1 = fma(gp[i], gq[i], g1);
+      else g0 = fma(gp[i], gq[i], g0);
+    }
+    const double gam = ring_sum<R>((g0 + g1) + (g2_ + g3)) * (dp * dq);
+    SEQM_TICK(1);
+    // tangent t = sgn(d) b / (|d| + sqrt(d^2 + b^2)), d = beta - alpha, b = 2 gamma, in FP32 with the approximate
+    // reciprocal square root / reciprocal (two MUFU instructions; |t| <= 1 up to their 1e-7)
+    const float df = (float)(aq - ap), bf = 2.0f * (float)gam;
+    const float h2 = fmaxf(fmaf(df, df, bf * bf), 1.0e-37f);
+    const float tf = (df >= 0.0f ? bf : -bf) * rcp_approx(fmaf(h2, rsqrt_approx(h2), fabsf(df)));
+    // columns already orthogonal to rounding are left alone: inside an exactly degenerate cluster gamma and the norm
+    // difference are both noise, the angle would be arbitrary, and such a rotation re-mixes the cluster's couplings to
+    // the other columns (the sweep then no longer converges quadratically; tools/proto/onesided_ring.py)
+    // (a small angle is harmless and is applied: it is what separates close but distinct eigenvalues)
+    const double g2 = gam * gam;
+    const bool noise = g2 <= (RING_COS_MIN * RING_COS_MIN) * (ap * aq) && fabsf(tf) > RING_T_NOISE;
+    const double t = (gam != 0.0 && !noise) ? (double)tf : 0.0;
+    const double tp = t * (dq * idp), tq = t * (dp * idq);
+    SEQM_TICK(2);
+    // the moving column leaves element by element as soon as it is rotated: the shuffles overlap the FMAs
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const double qn = fma(tq, gp[i], gq[i]);
+      gp[i] = fma(-tp, gq[i], gp[i]);
+      gq[i] = __shfl_sync(FULL, qn, from);
+    }
+    SEQM_TICK(3);
+    off += g2;
+    const double tt = t * t, q = tt + 1.0;
+    const double c = rsqrt_unit(q), ic = q * c;
+    // norms after the rotation, exact for ANY t (the shortcut alpha - t gamma holds for the exact tangent only and
+    // loses the difference of nearly degenerate columns when t comes from FP32)
+    const double c2 = c * c, tg2 = (t + t) * gam;
+    const double ap_n = c2 * (fma(tt, aq, ap) - tg2), aq_n = c2 * (fma(tt, ap, aq) + tg2);
+    dp *= c; idp *= ic;
+    ap = ap_n;
+    SEQM_TICK(4);
+    dq = __shfl_sync(FULL, dq * c, from);
+    idq = __shfl_sync(FULL, idq * ic, from);
+    aq = __shfl_sync(FULL, aq_n, from);
+    SEQM_TICK(5);
+  }
+
+  // the two halves of a group of processors exchange one column inside the warp: all P's to the first half, all Q's to
+  // the second; xm = lane distance of the partner processor
+  __device__ __forceinline__ void exchange(bool first, int xm) {
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const double got = __shfl_xor_sync(FULL, first ? gq[i] : gp[i], xm);
+      gq[i] = first ? got : gq[i];
+      gp[i] = first ? gp[i] : got;
+    }
+    const double g_d = __shfl_xor_sync(FULL, first ? dq : dp, xm);
+    const double g_i = __shfl_xor_sync(FULL, first ? idq : idp, xm);
+    const double g_a = __shfl_xor_sync(FULL, first ? aq : ap, xm);
+    dq = first ? g_d : dq; idq = first ? g_i : idq; aq = first ? g_a : aq;
+    dp = first ? dp : g_d; idp = first ? idp : g_i; ap = first ? ap : g_a;
+  }
+
+  // Kg rounds of a ring of Kg processors (P stays, Q moves on by one processor after every round but the last)
+  __device__ __forceinline__ void ring(int Kg, int kw, int h, int lane) {
+    const int src = (((kw & ~(Kg - 1)) | ((kw - 1) & (Kg - 1))) * R) + h;      // previous processor of the group, same row part
+#pragma unroll 1
+    for (int r = 0; r < Kg; ++r) rotate(r + 1 < Kg ? src : lane);
+  }
+
+  // all pairs among the 2 * K0 columns held by the K0 processors of one warp (kw = processor index inside the warp):
+  // phases of group size K0, K0/2, .., 1.  ONE copy of the round in the instruction stream (the one-launch SCF kernel
+  // around it is large and its warps run different phases: unrolled phases showed as no_instruction stalls)
+  __device__ __forceinline__ void phases(int K0, int kw, int h, int lane) {
+#pragma unroll 1
+    for (int Kg = K0; Kg >= 1; Kg >>= 1) {
+      ring(Kg, kw, h, lane);
+      if (Kg > 1) exchange((kw & (Kg >> 1)) == 0, (Kg >> 1) * R);
+    }
+  }
+};
+
 // Eigen-decomposition of one packed symmetric matrix by one warp and the density matrix of its lowest `no` eigenvectors.
 //   in : S0 = the N x LD rows of the matrix (only rows / columns < m are used); Vg = this molecule's eigenvector store
 //        [32][32] (row, slot) or null; warm != 0: start from the eigenvectors kept there by the previous call
@@ -104,7 +212,8 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
     sigma = w - lo;      // spectrum of A + sigma I within [w, 2w]
   }
 
-  double gp[H], gq[H];
+  RingCols<H, R> C;
+  double (&gp)[H] = C.gp, (&gq)[H] = C.gq;
   if (warm && Vg) {
     // V0 -> S1 (row, slot), G = (A + sigma I) V0
     {
@@ -151,116 +260,21 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
   __syncwarp();
   SEQM_PHASE(7);
 
-  double dp = 1.0, idp = 1.0, dq = 1.0, idq = 1.0, ap = 0.0, aq = 0.0;
-  // fold the scales into the columns and recompute the norms exactly
-  auto renorm = [&]() {
-    double sp_ = 0.0, sq_ = 0.0;
-#pragma unroll
-    for (int i = 0; i < H; ++i) {
-      gp[i] *= dp;
-      gq[i] *= dq;
-      sp_ = fma(gp[i], gp[i], sp_);
-      sq_ = fma(gq[i], gq[i], sq_);
-    }
-    ap = ring_sum<R>(sp_);
-    aq = ring_sum<R>(sq_);
-    dp = idp = dq = idq = 1.0;
-  };
-
-  double off = 0.0;
-  // one rotation of the columns P, Q of this processor; SHIFT: the rotated Q column then moves on to the lane `from`
-  auto rotate = [&](auto shift_tag, int from) {
-    constexpr bool SHIFT = decltype(shift_tag)::value;
-    SEQM_TICK(0);
-    double g0 = 0.0, g1 = 0.0;
-#pragma unroll
-    for (int i = 0; i < H; ++i) {
-      if (i & 1) g1 = fma(gp[i], gq[i], g1);
-      else g0 = fma(gp[i], gq[i], g0);
-    }
-    const double gam = ring_sum<R>(g0 + g1) * (dp * dq);
-    SEQM_TICK(1);
-    // tangent t = sgn(d) b / (|d| + sqrt(d^2 + b^2)), d = beta - alpha, b = 2 gamma, in FP32 with the approximate
-    // reciprocal square root / reciprocal (two MUFU instructions; |t| <= 1 up to their 1e-7)
-    const float df = (float)(aq - ap), bf = 2.0f * (float)gam;
-    const float h2 = fmaxf(fmaf(df, df, bf * bf), 1.0e-37f);
-    const float tf = (df >= 0.0f ? bf : -bf) * rcp_approx(fmaf(h2, rsqrt_approx(h2), fabsf(df)));
-    // columns already orthogonal to rounding are left alone: inside an exactly degenerate cluster gamma and the norm
-    // difference are both noise, the angle would be arbitrary, and such a rotation re-mixes the cluster's couplings to
-    // the other columns (the sweep then no longer converges quadratically; tools/proto/onesided_ring.py)
-    // (a small angle is harmless and is applied: it is what separates close but distinct eigenvalues)
-    const double g2 = gam * gam;
-    const bool noise = g2 <= (RING_COS_MIN * RING_COS_MIN) * (ap * aq) && fabsf(tf) > RING_T_NOISE;
-    const double t = (gam != 0.0 && !noise) ? (double)tf : 0.0;
-    const double tp = t * (dq * idp), tq = t * (dp * idq);
-    SEQM_TICK(2);
-    // the moving column leaves element by element as soon as it is rotated: the shuffles overlap the FMAs
-#pragma unroll
-    for (int i = 0; i < H; ++i) {
-      const double qn = fma(tq, gp[i], gq[i]);
-      gp[i] = fma(-tp, gq[i], gp[i]);
-      if constexpr (SHIFT) gq[i] = __shfl_sync(FULL, qn, from);
-      else gq[i] = qn;
-    }
-    SEQM_TICK(3);
-    off += g2;
-    const double tt = t * t, q = tt + 1.0;
-    const double c = rsqrt_unit(q), ic = q * c;
-    // norms after the rotation, exact for ANY t (the shortcut alpha - t gamma holds for the exact tangent only and
-    // loses the difference of nearly degenerate columns when t comes from FP32)
-    const double c2 = c * c, tg2 = (t + t) * gam;
-    const double ap_n = c2 * (fma(tt, aq, ap) - tg2), aq_n = c2 * (fma(tt, ap, aq) + tg2);
-    dp *= c; idp *= ic;
-    ap = ap_n;
-    SEQM_TICK(4);
-    if constexpr (SHIFT) {
-      dq = __shfl_sync(FULL, dq * c, from);
-      idq = __shfl_sync(FULL, idq * ic, from);
-      aq = __shfl_sync(FULL, aq_n, from);
-    } else {
-      dq *= c; idq *= ic;
-      aq = aq_n;
-    }
-    SEQM_TICK(5);
-  };
-  // the two halves of a group of Kg processors exchange one column: all P's to the first half, all Q's to the second
-  auto exchange = [&](int half) {
-    const bool first = (k & half) == 0;
-    const int xm = half * R;
-#pragma unroll
-    for (int i = 0; i < H; ++i) {
-      const double got = __shfl_xor_sync(FULL, first ? gq[i] : gp[i], xm);
-      gq[i] = first ? got : gq[i];
-      gp[i] = first ? gp[i] : got;
-    }
-    const double g_d = __shfl_xor_sync(FULL, first ? dq : dp, xm);
-    const double g_i = __shfl_xor_sync(FULL, first ? idq : idp, xm);
-    const double g_a = __shfl_xor_sync(FULL, first ? aq : ap, xm);
-    dq = first ? g_d : dq; idq = first ? g_i : idq; aq = first ? g_a : aq;
-    dp = first ? dp : g_d; idp = first ? idp : g_i; ap = first ? ap : g_a;
-  };
-
+  C.dp = C.idp = C.dq = C.idq = 1.0;
+  C.ap = C.aq = 0.0;
   int sweeps = 0;
   for (; sweeps < WARP_MAX_SWEEPS;) {
-    renorm();
-    off = 0.0;
-    const double tot = ap * ap + aq * aq;
-    // phases: ONE copy of the round in the instruction stream (the one-launch SCF kernel around this function is large
-    // and its warps run different phases: instruction-cache misses showed as no_instruction stalls when the phases
-    // were unrolled); the round that ends a phase shuffles from the own lane
-#pragma unroll 1
-    for (int Kg = K; Kg >= 1; Kg >>= 1) {
-      const int src = (((k & ~(Kg - 1)) | ((k - 1) & (Kg - 1))) * R) + h;      // previous processor of the group, same row part
-#pragma unroll 1
-      for (int r = 0; r < Kg; ++r) rotate(std::true_type{}, r + 1 < Kg ? src : lane);
-      if (Kg > 1) exchange(Kg >> 1);
-    }
+    C.renorm();
+    C.off = 0.0;
+    const double tot = C.ap * C.ap + C.aq * C.aq;
+    C.phases(K, k, h, lane);
     ++sweeps;
     // every lane of a processor carries the same off / tot
-    const double off2 = 2.0 * warp_sum(off), tot2 = warp_sum(tot);
+    const double off2 = 2.0 * warp_sum(C.off), tot2 = warp_sum(tot);
     if (off2 <= tol * tot2) break;
   }
-  renorm();
+  C.renorm();
+  const double ap = C.ap, aq = C.aq;
   SEQM_PHASE(8);
 
   // ---- eigenvalues, ranking (owner lane of slot s: processor s / 2, row part s % 2)

@@ -1,0 +1,289 @@
+// K3a for packed sizes 32 < m <= 64: the one-sided ring Jacobi of eigh_ring.cuh on TWO warps per molecule.
+// 64 column slots on 32 processors of 2 lanes (a lane holds H = N / 2 rows of its processor's columns P and Q in
+// registers, 2H <= 64 doubles); processors 0..15 live in warp 0, 16..31 in warp 1.  A sweep of 63 rounds:
+//   1. ring of 16 inside each warp (16 rounds): every P of a warp meets every Q of that warp;
+//   2. the warps swap their Q columns through shared memory (ONE block barrier pair), ring of 16 again: now every P
+//      has met all 32 Q's;
+//   3. all P's go to warp 0, all Q's to warp 1 (second and last exchange through shared memory);
+//   4. each warp finishes its own 32 columns with the recursive phases 16, 8, 4, 2, 1 (31 rounds) without any
+//      synchronisation between the warps.
+// So the warps meet twice per sweep (plus once for the convergence sums); everything else is registers and shuffles.
+// The shared-memory (CTA) Jacobi this replaces moved ~6 m^2 doubles through shared memory per round behind two block
+// barriers: 73 % of the config-4 sweep at 13 % FP64-pipe utilisation (profiles/r01q_grad_eigh_ncu.txt).
+// Shared memory: one N x (N + 2) buffer = the matrix at the start, the exchange buffer during the sweeps, the weighted
+// occupied eigenvectors for P = 2 W W^T at the end.  The warm start G = (A + sigma I) V0 streams V0 from the caller's
+// eigenvector store (L2) against A in shared memory.
+// reference: seqm/seqm_functions/diag.py:102-172 (sym_eig_trunc, construct_P), pack.py:7-41
+#include "eigh_ring.cuh"
+#include "dgemm.cuh"
+
+namespace seqm {
+
+constexpr int RING2_SLOTS = 64;      // column slots = row stride of the eigenvector store of this kernel
+
+template <int N>
+__global__ void __launch_bounds__(64, 5)
+eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
+                  const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
+                  const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
+                  double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm,
+                  double tol) {
+  constexpr int H = N / 2, R = 2, LD = N + 2;
+  static_assert(N % 2 == 0 && N > 32 && N <= 64, "packed size handled by two warps");
+  extern __shared__ __align__(16) double sm[];
+  double* S0 = sm;                       // [N][LD]
+  double* red = sm + N * LD;             // [8] block reductions
+  const int mol = blockIdx.x;
+  if (active && !active[mol]) return;
+  const int nh4 = 4 * nheavy[mol];
+  const int m = nh4 + nhydro[mol];
+  if (m <= 0) return;
+  const int no = nocc[mol];
+  const int n4 = 4 * S;
+  const size_t base = (size_t)mol * n4 * n4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int k = tid >> 1, kw = k & 15, h = tid & 1;      // processor, processor inside the warp, row part
+  const int row0 = h * H;
+  const int sP = 2 * k;
+  double* Vg = Vstore ? Vstore + (size_t)mol * N * RING2_SLOTS : nullptr;
+
+  // ---- the packed matrix (upper triangle, like eigh(UPLO='U')), both triangles, into shared memory
+  for (int r = 0; r < N; ++r) {
+    double x = 0.0;
+    if (r < m && tid < m) {
+      const int rr = r <= tid ? r : tid, cc = r <= tid ? tid : r;
+      x = F[base + (size_t)pk2pd(rr, nh4) * n4 + pk2pd(cc, nh4)];
+    }
+    if (tid < N) S0[r * LD + tid] = x;
+  }
+  __syncthreads();
+  // ---- Gershgorin bounds -> shift
+  double sigma;
+  {
+    double lo = 1.0e300, hi = -1.0e300;
+    if (tid < m) {
+      double rad = 0.0, aii = 0.0;
+      for (int j = 0; j < m; ++j) {
+        const double x = S0[j * LD + tid];      // column tid = row tid
+        if (j == tid) aii = x; else rad += fabs(x);
+      }
+      lo = aii - rad;
+      hi = aii + rad;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = fmin(lo, __shfl_xor_sync(FULL, lo, o));
+      hi = fmax(hi, __shfl_xor_sync(FULL, hi, o));
+    }
+    if (lane == 0) { red[2 * warp] = lo; red[2 * warp + 1] = hi; }
+    __syncthreads();
+    lo = fmin(red[0], red[2]);
+    hi = fmax(red[1], red[3]);
+    const double w = fmax(hi - lo, 1.0);
+    sigma = w - lo;      // spectrum of A + sigma I within [w, 2w]
+  }
+
+  // ---- G = (A + sigma I) V0, this lane's H rows of the columns P, Q of its processor
+  RingCols<H, R> C;
+  double (&gp)[H] = C.gp, (&gq)[H] = C.gq;
+  if (warm && Vg) {
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const double2 x = *reinterpret_cast<const double2*>(&Vg[(row0 + i) * RING2_SLOTS + sP]);
+      gp[i] = sigma * x.x;
+      gq[i] = sigma * x.y;
+    }
+    double2 va = *reinterpret_cast<const double2*>(&Vg[0 * RING2_SLOTS + sP]);
+    double2 vb = *reinterpret_cast<const double2*>(&Vg[1 * RING2_SLOTS + sP]);
+#pragma unroll 1
+    for (int jj = 0; jj < N / 2; ++jj) {
+      const double2 ca = va, cb = vb;
+      if (jj + 1 < N / 2) {      // next two rows of V0 on their way while this pair is used
+        va = *reinterpret_cast<const double2*>(&Vg[(2 * jj + 2) * RING2_SLOTS + sP]);
+        vb = *reinterpret_cast<const double2*>(&Vg[(2 * jj + 3) * RING2_SLOTS + sP]);
+      }
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const double2 a2 = *reinterpret_cast<const double2*>(&S0[(row0 + i) * LD + 2 * jj]);
+        gp[i] = fma(a2.x, ca.x, gp[i]);
+        gq[i] = fma(a2.x, ca.y, gq[i]);
+        gp[i] = fma(a2.y, cb.x, gp[i]);
+        gq[i] = fma(a2.y, cb.y, gq[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < H; ++i) {      // rows beyond m carry nothing (A and V0 are zero there; keep it exact)
+      if (row0 + i >= m) { gp[i] = 0.0; gq[i] = 0.0; }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const int row = row0 + i;
+      // A symmetric: column s = row s; slots beyond m (and beyond the N rows held in shared memory) are empty
+      const double xp = (row < m && sP < m) ? S0[sP * LD + row] : 0.0;
+      const double xq = (row < m && sP + 1 < m) ? S0[(sP + 1) * LD + row] : 0.0;
+      gp[i] = xp + ((row == sP && sP < m) ? sigma : 0.0);
+      gq[i] = xq + ((row == sP + 1 && sP + 1 < m) ? sigma : 0.0);
+    }
+  }
+  __syncthreads();      // the matrix is consumed: S0 is the exchange buffer from here on
+  double* X = S0;       // [H + 3][64]
+
+  C.dp = C.idp = C.dq = C.idq = 1.0;
+  C.ap = C.aq = 0.0;
+  int sweeps = 0;
+  for (; sweeps < WARP_MAX_SWEEPS;) {
+    C.renorm();
+    C.off = 0.0;
+    const double tot = C.ap * C.ap + C.aq * C.aq;
+    // 1. every P of a warp meets every Q of that warp
+    C.ring(16, kw, h, lane);
+    // 2. the warps swap their Q columns; ring again
+#pragma unroll
+    for (int i = 0; i < H; ++i) X[i * 64 + tid] = gq[i];
+    X[H * 64 + tid] = C.dq; X[(H + 1) * 64 + tid] = C.idq; X[(H + 2) * 64 + tid] = C.aq;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < H; ++i) gq[i] = X[i * 64 + (tid ^ 32)];
+    C.dq = X[H * 64 + (tid ^ 32)]; C.idq = X[(H + 1) * 64 + (tid ^ 32)]; C.aq = X[(H + 2) * 64 + (tid ^ 32)];
+    __syncthreads();
+    C.ring(16, kw, h, lane);
+    // 3. all P's to warp 0 (into its Q slots), all Q's to warp 1 (into its P slots)
+    if (warp == 0) {
+#pragma unroll
+      for (int i = 0; i < H; ++i) X[i * 64 + tid] = gq[i];
+      X[H * 64 + tid] = C.dq; X[(H + 1) * 64 + tid] = C.idq; X[(H + 2) * 64 + tid] = C.aq;
+    } else {
+#pragma unroll
+      for (int i = 0; i < H; ++i) X[i * 64 + tid] = gp[i];
+      X[H * 64 + tid] = C.dp; X[(H + 1) * 64 + tid] = C.idp; X[(H + 2) * 64 + tid] = C.ap;
+    }
+    __syncthreads();
+    if (warp == 0) {
+#pragma unroll
+      for (int i = 0; i < H; ++i) gq[i] = X[i * 64 + (tid ^ 32)];
+      C.dq = X[H * 64 + (tid ^ 32)]; C.idq = X[(H + 1) * 64 + (tid ^ 32)]; C.aq = X[(H + 2) * 64 + (tid ^ 32)];
+    } else {
+#pragma unroll
+      for (int i = 0; i < H; ++i) gp[i] = X[i * 64 + (tid ^ 32)];
+      C.dp = X[H * 64 + (tid ^ 32)]; C.idp = X[(H + 1) * 64 + (tid ^ 32)]; C.ap = X[(H + 2) * 64 + (tid ^ 32)];
+    }
+    // 4. each warp finishes its own 32 columns
+    C.phases(16, kw, h, lane);
+    ++sweeps;
+    // every lane of a processor carries the same off / tot
+    const double offw = warp_sum(C.off), totw = warp_sum(tot);
+    if (lane == 0) { red[4 + 2 * warp] = offw; red[5 + 2 * warp] = totw; }
+    __syncthreads();      // also: everybody has read X before the next sweep writes it
+    const double off2 = 2.0 * (red[4] + red[6]), tot2 = red[5] + red[7];
+    __syncthreads();
+    if (off2 <= tol * tot2) break;
+  }
+  C.renorm();
+  const double ap = C.ap, aq = C.aq;
+
+  // ---- eigenvalues and ranking: slot tid = column P (h = 0) or Q (h = 1) of processor k
+  double* ev = red + 8;      // [64]
+  const double amine = h ? aq : ap;
+  const bool real = amine > 0.0;
+  const double e = real ? sqrt(amine) - sigma : 0.0;
+  ev[tid] = real ? e : 1.0e300;
+  __syncthreads();
+  int rank = 0;
+#pragma unroll 8
+  for (int p = 0; p < 64; ++p) {
+    const double ep = ev[p];
+    if (ep < 1.0e299 && (ep < e || (ep == e && p < tid))) ++rank;
+  }
+  if (e_out) {
+    double* eo = e_out + (size_t)mol * n4;
+    if (real) eo[rank] = e;
+    for (int i = m + tid; i < n4; i += 64) eo[i] = 0.0;
+  }
+  const int rankP = __shfl_sync(FULL, rank, lane & ~1), rankQ = __shfl_sync(FULL, rank, lane | 1);
+  const bool realP = ap > 0.0, realQ = aq > 0.0;
+  const int ncw = no < m ? no : m;      // occupied columns
+  // ---- eigenvectors = normalised columns: kept for the next call, reference-order output, occupied columns -> S0
+  const double nP = realP ? rsqrt(ap) : 0.0, nQ = realQ ? rsqrt(aq) : 0.0;
+  double* W = S0;      // [N][LD], column = rank
+  for (int idx = tid; idx < N * LD; idx += 64) W[idx] = 0.0;
+  __syncthreads();
+  double* vo = v_out ? v_out + base : nullptr;
+#pragma unroll
+  for (int i = 0; i < H; ++i) {
+    const int row = row0 + i;
+    const double vp = gp[i] * nP, vq = gq[i] * nQ;
+    if (Vg) *reinterpret_cast<double2*>(&Vg[row * RING2_SLOTS + sP]) = make_double2(vp, vq);
+    if (vo && row < m) {
+      if (realP) vo[(size_t)row * n4 + rankP] = vp;
+      if (realQ) vo[(size_t)row * n4 + rankQ] = vq;
+    }
+    if (realP && rankP < ncw) W[row * LD + rankP] = vp;
+    if (realQ && rankQ < ncw) W[row * LD + rankQ] = vq;
+  }
+  __syncthreads();
+  // ---- P = 2 W W^T: thread = row, the occupied columns in two chunks of 32
+  for (int c0 = 0; c0 < ncw; c0 += 32) {
+    const int rowoff = (tid < N ? tid : 0) * LD + c0;
+    double w[32];
+#pragma unroll
+    for (int jj = 0; jj < 16; ++jj) {
+      const bool in = c0 + 2 * jj < N;      // W has N columns (+2 pad, zero)
+      const double2 x = in ? *reinterpret_cast<const double2*>(&W[rowoff + 2 * jj]) : make_double2(0.0, 0.0);
+      w[2 * jj] = x.x;
+      w[2 * jj + 1] = x.y;
+    }
+    const int nc = ncw - c0 < 32 ? ncw - c0 : 32;
+#pragma unroll 2
+    for (int i2 = 0; i2 < m; ++i2) {
+      double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+      for (int jj = 0; jj < 16; ++jj) {
+        if (2 * jj < nc) {
+          const double2 x = *reinterpret_cast<const double2*>(&W[i2 * LD + c0 + 2 * jj]);
+          acc0 = fma(w[2 * jj], x.x, acc0);
+          acc1 = fma(w[2 * jj + 1], x.y, acc1);
+        }
+      }
+      if (tid < m) {      // P[tid][i2] == P[i2][tid]
+        double* dst = &P[base + (size_t)pk2pd(i2, nh4) * n4 + pk2pd(tid, nh4)];
+        const double val = 2.0 * (acc0 + acc1);
+        *dst = c0 == 0 ? val : *dst + val;
+      }
+    }
+  }
+  if (info && tid == 0) info[mol] = sweeps;
+}
+
+size_t eigh_ring2_vstore_doubles(int64_t nmol) { return (size_t)nmol * 64 * RING2_SLOTS; }
+
+template <int N>
+static int launch_ring2_n(int64_t nmol, int S, const double* F, const int32_t* nheavy, const int32_t* nhydro,
+                          const int32_t* nocc, const uint8_t* active, double* P, double* e_out, double* v_out,
+                          int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
+  constexpr int H = N / 2, LD = N + 2;
+  constexpr size_t cells = (size_t)N * LD > (size_t)64 * (H + 3) ? (size_t)N * LD : (size_t)64 * (H + 3);
+  constexpr size_t smem = (cells + 8 + 64) * sizeof(double);
+  static_assert(smem <= 48 * 1024, "fits the default dynamic shared memory limit");
+  eigh_ring2_kernel<N><<<(unsigned)nmol, 64, smem, st>>>(S, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore,
+                                                       warm, tol);
+  SEQM_CHECK_LAUNCH("eigh_ring2_kernel");
+  return SEQM_OK;
+}
+
+// mp = even padded size, 32 < mp <= 64
+int launch_eigh_ring2(int64_t nmol, int64_t molsize, int mp, const double* F, const int32_t* nheavy,
+                      const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P, double* e_out,
+                      double* v_out, int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
+#define SEQM_RING2_CASE(NN)                                                                                          \
+  if (mp <= NN)                                                                                                      \
+    return launch_ring2_n<NN>(nmol, (int)molsize, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore, warm, tol, st)
+  SEQM_RING2_CASE(40);
+  SEQM_RING2_CASE(48);
+  SEQM_RING2_CASE(56);
+  SEQM_RING2_CASE(64);
+#undef SEQM_RING2_CASE
+  return fail(SEQM_EUNSUPPORTED, "launch_eigh_ring2: packed size above 64");
+}
+
+}  // namespace seqm

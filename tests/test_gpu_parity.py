@@ -92,9 +92,10 @@ def test_eigh_kernels_random(force_block):
         assert float((C.T @ C - torch.eye(m)).abs().max()) < 1e-13
 
 
-@pytest.mark.parametrize('mmax', [2, 7, 12, 15, 20, 23, 27, 30, 32])
+@pytest.mark.parametrize('mmax', [2, 7, 12, 15, 20, 23, 27, 30, 32, 33, 40, 47, 48, 55, 56, 63, 64])
 def test_eigh_warp_kernel_sizes(mmax):
-    """every instantiation of the warp Jacobi kernel (padded sizes 8..32) on batches of mixed sizes <= mmax"""
+    """every instantiation of the ring Jacobi kernels (one warp: padded sizes 8..32, two warps: 40..64) on batches of
+    mixed sizes <= mmax"""
     from pyseqm_b200 import _ops
     import seqm_oracle as orc
     dev = _dev()
