@@ -24,9 +24,36 @@ import sys
 import threading
 import time
 
-# torchrun exports OMP_NUM_THREADS=1; the CPU baseline legs (rank 0) must use the host cores the line reports
+
+
+def host_cores():
+    """host threads this process may really use: the scheduler affinity, capped by the cgroup CPU quota (a container
+    that sees 24 CPUs but is limited to fewer runs a 24-thread OpenMP region 40x slower than one sized to its quota)"""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    try:
+        with open('/sys/fs/cgroup/cpu.max') as f:
+            quota, period = f.read().split()[:2]
+        if quota != 'max':
+            n = min(n, max(1, int(float(quota) / float(period))))
+    except Exception:
+        try:
+            with open('/sys/fs/cgroup/cpu/cpu.cfs_quota_us') as f:
+                q = int(f.read())
+            with open('/sys/fs/cgroup/cpu/cpu.cfs_period_us') as f:
+                per = int(f.read())
+            if q > 0:
+                n = min(n, max(1, q // per))
+        except Exception:
+            pass
+    return max(1, n)
+
+
+# torchrun exports OMP_NUM_THREADS=1; the CPU legs (rank 0) must use the host cores the line reports
 if os.environ.get('OMP_NUM_THREADS') == '1' and int(os.environ.get('RANK', '0')) == 0:
-    os.environ['OMP_NUM_THREADS'] = str(os.cpu_count() or 1)
+    os.environ['OMP_NUM_THREADS'] = str(host_cores())
 
 import numpy as np
 import torch
@@ -138,7 +165,7 @@ class CpuPath:
         warnings.filterwarnings('ignore')
         self.seqm = load_reference()
         self.kind = 'reference' if self.seqm is not None else 'port'
-        self.cores = os.cpu_count() or 1
+        self.cores = host_cores()
         torch.set_num_threads(self.cores)
         if self.seqm is None:
             sys.path.insert(0, os.path.join(ROOT, 'oracle'))
@@ -321,9 +348,10 @@ def time_op(fn, flush, reps=5):
 def run_gpu(ctx):
     """BASELINE.json configs[1]: the headline workload.  -> result dict on rank 0, None elsewhere"""
     from pyseqm_b200 import _lib, _ops, synth
-    from pyseqm_b200.basics import Force
+    from pyseqm_b200.basics import Force, GraphedForce
     from pyseqm_b200.seqm_functions.constants import Constants
     args, rank, world, dev = ctx.args, ctx.rank, ctx.world, ctx.dev
+    use_graph = os.environ.get('SEQM_BENCH_GRAPH', '1') != '0'
     if world > 1:
         import torch.distributed as dist
         from pyseqm_b200.distributed import gather_molecules
@@ -343,8 +371,11 @@ def run_gpu(ctx):
 
     pending = []
 
-    def step(x):
-        out = force_mod(const, x, species)
+    graphed = GraphedForce(dict(SEQM_PAR)).to(dev) if use_graph else None
+
+    def step(x, eager=False):
+        # one Force call over the batch: a CUDA-graph replay of the call (pyseqm_b200.basics.GraphedForce) unless eager
+        out = force_mod(const, x, species) if (eager or graphed is None) else graphed(const, x, species)
         if world > 1:
             # energies of every shard in global molecule order: one preallocated all_gather_into_tensor, asynchronous on
             # NCCL's stream; the result of step k is consumed (waited for) while step k+1 is already enqueued
@@ -365,9 +396,16 @@ def run_gpu(ctx):
     Force(dict(SEQM_PAR)).to(dev)(const, coords[:8].clone(), species[:8].clone())
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    out = step(coords.clone())
+    out = step(coords.clone(), eager=True)
     torch.cuda.synchronize()
     cold_ms = (time.perf_counter() - t0) * 1e3
+    # library launches of one call (a graph replay re-issues exactly the launches of the captured call; the library's
+    # counter only sees the capture)
+    force_mod.flush_status()
+    lc0 = L.seqm_launch_count()
+    step(coords.clone(), eager=True)
+    drain()
+    launches_per_call = int(L.seqm_launch_count() - lc0)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -390,7 +428,7 @@ def run_gpu(ctx):
         evs.append((a, b))
     drain()
     barrier()
-    launches = int(L.seqm_launch_count() - l0)
+    launches = int(L.seqm_launch_count() - l0) if graphed is None else launches_per_call * args.steps
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
     log("benzene: per-step ms " + " ".join("%.3f" % a.elapsed_time(b) for a, b in evs))
     # ---- end to end: pinned host coordinates in, forces + energies out, every step ----
@@ -460,13 +498,16 @@ def run_gpu(ctx):
                                 "mostly idle, stalls short_scoreboard / wait / long_scoreboard - DESIGN.md section 6)",
                      "algorithmic_tflops": flops / (kernels[top]["ms_per_launch"] * 1e-3) / 1e12,
                      "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
-    log("benzene: cpu baseline")
-    # ---- CPU baseline: the reference's CPU path (oracle/_ref, else the oracle port) on this rank's batch ----
-    cpu = CpuPath()
-    ns, reps = NMOL, 2
-    cpu.force_seconds(sp[:64], xyz[:64], 'AM1', elements=(0, 1, 6))
-    cpu_s = sum(cpu.force_seconds(sp, xyz, 'AM1', elements=(0, 1, 6)) for _ in range(reps)) / reps
-    cores = cpu.cores
+    # ---- CPU baseline (rank 0, N = 1 only): the reference's CPU path (oracle/_ref, else the oracle port) on this batch ----
+    cpu_base = None
+    if world == 1:
+        log("benzene: cpu baseline")
+        cpu = CpuPath()
+        ns, reps = NMOL, 2
+        cpu.force_seconds(sp[:64], xyz[:64], 'AM1', elements=(0, 1, 6))
+        cpu_s = sum(cpu.force_seconds(sp, xyz, 'AM1', elements=(0, 1, 6)) for _ in range(reps)) / reps
+        cpu_base = {"value": ns / cpu_s, "unit": "molecules/s", "cores": cpu.cores, "kind": cpu.kind,
+                    "sample": "the %d benzenes of rank 0, %d Force calls" % (ns, reps)}
     ms_step = total_ms / args.steps
     nm_total = NMOL * world
     return ({
@@ -476,8 +517,11 @@ def run_gpu(ctx):
         "config": {"workload": WORKLOAD_BENZENE,
                    "molecules_per_gpu": NMOL, "l2": "192 MiB buffer written between timed steps",
                    "scf_not_converged": nconv_fail, "scf_iterations": int(st['iterations']),
-                   "api": "pyseqm_b200.basics.Force with defer_scf_warning=True (SCF status of a call read at the next "
-                          "call); N > 1: asynchronous gather of the energies, consumed one step later"},
+                   "api": ("pyseqm_b200.basics.GraphedForce: one Force call (pair pass, one-launch SCF, adjoint, energies) "
+                           "replayed as one CUDA graph per step; gpu_launches = kernels of the captured call x steps"
+                           if graphed is not None else
+                           "pyseqm_b200.basics.Force with defer_scf_warning=True (SCF status of a call read at the next "
+                           "call)") + "; N > 1: asynchronous gather of the energies, consumed one step later"},
         "cold_call_ms": cold_ms,
         "cold_call_note": "first Force call with a new species tensor (Parser, parameter gather, topology, per-atom "
                           "records, initial guess built and cached), CUDA context already up; steady state is ms_per_step",
@@ -485,8 +529,7 @@ def run_gpu(ctx):
                 "h2d_bytes_per_step": NMOL * 12 * 3 * 8, "d2h_bytes_per_step": NMOL * 12 * 3 * 8 + NMOL * 8},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "kernels": kernels,
         "profile_one_step": prof,
-        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": cpu.kind,
-                         "sample": "the %d benzenes of rank 0, %d Force calls" % (ns, reps)}})
+        "cpu_baseline": cpu_base})
 
 
 def run_c60xl(ctx):
@@ -600,11 +643,12 @@ def run_c60xl(ctx):
             kernels[nm_] = {"ms_per_launch": ms_, "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / (ms_ * 1e-3) / 1e9,
                             "frac_of_hbm": nbytes / (ms_ * 1e-3) / 1e9 / hbm}
     ms_step = total_ms / args.steps
-    log("xlbomd: cpu baseline")
-    cpu = CpuPath()
-    spc, xyzc = synth.c60(2, seed=0)
-    xl_s = cpu.xlbomd_seconds_per_step(spc, xyzc, 3)
-    cpu_base = None
+    cpu_base, xl_s = None, None
+    if world == 1:      # CPU baselines are an N = 1 item
+        log("xlbomd: cpu baseline")
+        cpu = CpuPath()
+        spc, xyzc = synth.c60(2, seed=0)
+        xl_s = cpu.xlbomd_seconds_per_step(spc, xyzc, 3)
     if xl_s:
         cpu_base = {"value": 1.0 / xl_s * (2.0 / nmol), "unit": "batch steps/s", "cores": cpu.cores, "kind": cpu.kind,
                     "sample": "XL_BOMD of the reference on 2 C60, 3 steady-state steps (initialisation subtracted), scaled "
@@ -841,11 +885,14 @@ def run_organics(ctx):
             "note": "algorithmic bytes of the whole sweep (integrals once + 4 packed matrices per molecule) over the sum of "
                     "the profiled kernel times of one sweep; the SCF kernels are latency / FP64-issue bound (DESIGN.md), "
                     "one-launch warp SCF %.1f ms of %.1f ms" % (small_ms, tot_prof)}
-    log("organics: cpu baseline")
-    cpu = CpuPath()
-    cores = cpu.cores
-    ns = 512
-    cpu_s = cpu.force_seconds(sp[:ns], xyz[:ns], 'MNDO')
+    cpu_base = None
+    if world == 1:      # CPU baselines are an N = 1 item
+        log("organics: cpu baseline")
+        cpu = CpuPath()
+        ns = 512
+        cpu_s = cpu.force_seconds(sp[:ns], xyz[:ns], 'MNDO')
+        cpu_base = {"value": ns / cpu_s, "unit": "molecules/s", "cores": cpu.cores, "kind": cpu.kind,
+                    "sample": "the first %d molecules of the sweep, one Force call" % ns}
     ms_step = total_ms / nsteps
     return ({
         "metric": "SCF molecules/sec", "value": ntotal / (ms_step * 1e-3), "unit": "molecules/s", "n_gpus": world,
@@ -860,8 +907,7 @@ def run_organics(ctx):
         "e2e": {"value": ntotal / (e2e_ms / nsteps * 1e-3), "unit": "molecules/s",
                 "h2d_bytes_per_step": nloc * 30 * 3 * 8, "d2h_bytes_per_step": nloc * 30 * 3 * 8 + nloc * 8},
         "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roof, "profile_one_step": prof,
-        "cpu_baseline": {"value": ns / cpu_s, "unit": "molecules/s", "cores": cores, "kind": cpu.kind,
-                         "sample": "the first %d molecules of the sweep, one Force call" % ns}})
+        "cpu_baseline": cpu_base})
 
 
 def main():
