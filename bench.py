@@ -494,8 +494,10 @@ def run_gpu(ctx):
         flops = B_ * iters * (9.0 * m_ ** 3 + 2.0 * m_ * m_ * int(topo.nocc.max()))      # 9 m^3 + 2 m^2 nocc per eigensolve
         traffic, tsrc = ncu_traffic('scf_small_benzene1024')
         roof.update({"traffic": traffic, "traffic_source": tsrc,
-                     "limiter": "latency of one warp per molecule (6.9 molecules per SM; ncu: FP64 pipe and issue slots "
-                                "mostly idle, stalls short_scoreboard / wait / long_scoreboard - DESIGN.md section 6)",
+                     "limiter": "latency of one warp per molecule (6.9 molecules per SM): the dependent chain of a ring-Jacobi "
+                                "round (dot product -> reduction -> tangent -> FMAs -> shuffles, ~600-800 cycles) and "
+                                "the L2 latency of the Fock / Pulay phases; ncu r02g/h: issue slots 34 %, FP64 pipe 22 %, "
+                                "stalls wait / long_scoreboard - DESIGN.md section 4",
                      "algorithmic_tflops": flops / (kernels[top]["ms_per_launch"] * 1e-3) / 1e12,
                      "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
     # ---- CPU baseline (rank 0, N = 1 only): the reference's CPU path (oracle/_ref, else the oracle port) on this batch ----
