@@ -107,9 +107,14 @@ class Pack_Parameters(torch.nn.Module):
                         parameters=self.required_list)
 
     def forward(self, Z, learned_params=dict()):
+        # a NEW dict: the reference fills the caller's dict in place (basics.py:148-154), which with the shared default
+        # argument `learned_parameters=dict()` of Energy / Force leaves the module-level default non-empty after the first
+        # call - here that would switch the cached-species path off for good and let BucketedBatch's worker threads
+        # overwrite each other's parameters
+        out = dict(learned_params)
         for i in range(self.nrp):
-            learned_params[self.required_list[i]] = self.p[Z, i]
-        return learned_params
+            out[self.required_list[i]] = self.p[Z, i]
+        return out
 
 
 class Hamiltonian(torch.nn.Module):

@@ -111,26 +111,29 @@ template <int H, int R> struct RingCols {
     const double t = (gam != 0.0 && !noise) ? (double)tf : 0.0;
     const double tp = t * (dq * idp), tq = t * (dp * idq);
     SEQM_TICK(2);
-    // the moving column leaves element by element as soon as it is rotated: the shuffles overlap the FMAs
+    // The rotation as two IN-PLACE shears (no temporaries, so no register copies around the 64-bit shuffles):
+    //   p <- p - tp q            (the scaled fast-Givens update of column P)
+    //   q <- q + tq c^2 p_new    (= (q + tq p_old) / (1 + t^2): the rotated column Q up to the factor 1 + t^2, which goes
+    //                             into its scale: d_q <- d_q / c instead of c d_q)
 #pragma unroll
-    for (int i = 0; i < H; ++i) {
-      const double qn = fma(tq, gp[i], gq[i]);
-      gp[i] = fma(-tp, gq[i], gp[i]);
-      gq[i] = __shfl_sync(FULL, qn, from);
-    }
-    SEQM_TICK(3);
+    for (int i = 0; i < H; ++i) gp[i] = fma(-tp, gq[i], gp[i]);
     off += g2;
     const double tt = t * t, q = tt + 1.0;
     const double c = rsqrt_unit(q), ic = q * c;
+    const double c2 = c * c, tq2 = tq * c2;
+    // the moving column leaves element by element as soon as it is rotated: the shuffles overlap the FMAs
+#pragma unroll
+    for (int i = 0; i < H; ++i) gq[i] = __shfl_sync(FULL, fma(tq2, gp[i], gq[i]), from);
+    SEQM_TICK(3);
     // norms after the rotation, exact for ANY t (the shortcut alpha - t gamma holds for the exact tangent only and
     // loses the difference of nearly degenerate columns when t comes from FP32)
-    const double c2 = c * c, tg2 = (t + t) * gam;
+    const double tg2 = (t + t) * gam;
     const double ap_n = c2 * (fma(tt, aq, ap) - tg2), aq_n = c2 * (fma(tt, ap, aq) + tg2);
     dp *= c; idp *= ic;
     ap = ap_n;
     SEQM_TICK(4);
-    dq = __shfl_sync(FULL, dq * c, from);
-    idq = __shfl_sync(FULL, idq * ic, from);
+    dq = __shfl_sync(FULL, dq * ic, from);
+    idq = __shfl_sync(FULL, idq * c, from);
     aq = __shfl_sync(FULL, aq_n, from);
     SEQM_TICK(5);
   }

@@ -17,12 +17,16 @@
 #include "eigh_ring.cuh"
 #include "dgemm.cuh"
 
+#ifndef SEQM_R2PHASE
+#define SEQM_R2PHASE(i)      // tools/time_ring2.cu accumulates clock64() per phase of block 0
+#endif
+
 namespace seqm {
 
 constexpr int RING2_SLOTS = 64;      // column slots = row stride of the eigenvector store of this kernel
 
 template <int N>
-__global__ void __launch_bounds__(64, 5)
+__global__ void __launch_bounds__(64, (N <= 40 ? 8 : (N <= 48 ? 6 : 5)))
 eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict__ nheavy,
                   const int32_t* __restrict__ nhydro, const int32_t* __restrict__ nocc,
                   const uint8_t* __restrict__ active, double* __restrict__ P, double* __restrict__ e_out,
@@ -47,16 +51,29 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   const int sP = 2 * k;
   double* Vg = Vstore ? Vstore + (size_t)mol * N * RING2_SLOTS : nullptr;
 
+  SEQM_R2PHASE(-1);
   // ---- the packed matrix (upper triangle, like eigh(UPLO='U')), both triangles, into shared memory
-  for (int r = 0; r < N; ++r) {
-    double x = 0.0;
-    if (r < m && tid < m) {
-      const int rr = r <= tid ? r : tid, cc = r <= tid ? tid : r;
-      x = F[base + (size_t)pk2pd(rr, nh4) * n4 + pk2pd(cc, nh4)];
+  {
+    const int ctid = pk2pd(tid < m ? tid : 0, nh4);
+#pragma unroll 1
+    for (int r0 = 0; r0 < N; r0 += 8) {      // eight rows per batch: eight independent loads in flight per thread
+      double x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int r = r0 + u;
+        x[u] = 0.0;
+        if (r < m && tid < m) {
+          const int cr = pk2pd(r, nh4);
+          x[u] = r <= tid ? F[base + (size_t)cr * n4 + ctid] : F[base + (size_t)ctid * n4 + cr];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (tid < N) S0[(r0 + u) * LD + tid] = x[u];
     }
-    if (tid < N) S0[r * LD + tid] = x;
   }
   __syncthreads();
+  SEQM_R2PHASE(0);
   // ---- Gershgorin bounds -> shift
   double sigma;
   {
@@ -83,6 +100,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
     sigma = w - lo;      // spectrum of A + sigma I within [w, 2w]
   }
 
+  SEQM_R2PHASE(1);
   // ---- G = (A + sigma I) V0, this lane's H rows of the columns P, Q of its processor
   RingCols<H, R> C;
   double (&gp)[H] = C.gp, (&gq)[H] = C.gq;
@@ -129,6 +147,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   __syncthreads();      // the matrix is consumed: S0 is the exchange buffer from here on
   double* X = S0;       // [H + 3][64]
 
+  SEQM_R2PHASE(2);
   C.dp = C.idp = C.dq = C.idq = 1.0;
   C.ap = C.aq = 0.0;
   int sweeps = 0;
@@ -182,6 +201,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   C.renorm();
   const double ap = C.ap, aq = C.aq;
 
+  SEQM_R2PHASE(3);
   // ---- eigenvalues and ranking: slot tid = column P (h = 0) or Q (h = 1) of processor k
   double* ev = red + 8;      // [64]
   const double amine = h ? aq : ap;
@@ -203,6 +223,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   const int rankP = __shfl_sync(FULL, rank, lane & ~1), rankQ = __shfl_sync(FULL, rank, lane | 1);
   const bool realP = ap > 0.0, realQ = aq > 0.0;
   const int ncw = no < m ? no : m;      // occupied columns
+  SEQM_R2PHASE(4);
   // ---- eigenvectors = normalised columns: kept for the next call, reference-order output, occupied columns -> S0
   const double nP = realP ? rsqrt(ap) : 0.0, nQ = realQ ? rsqrt(aq) : 0.0;
   double* W = S0;      // [N][LD], column = rank
@@ -222,36 +243,48 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
     if (realQ && rankQ < ncw) W[row * LD + rankQ] = vq;
   }
   __syncthreads();
-  // ---- P = 2 W W^T: thread = row, the occupied columns in two chunks of 32
-  for (int c0 = 0; c0 < ncw; c0 += 32) {
-    const int rowoff = (tid < N ? tid : 0) * LD + c0;
-    double w[32];
-#pragma unroll
-    for (int jj = 0; jj < 16; ++jj) {
-      const bool in = c0 + 2 * jj < N;      // W has N columns (+2 pad, zero)
-      const double2 x = in ? *reinterpret_cast<const double2*>(&W[rowoff + 2 * jj]) : make_double2(0.0, 0.0);
-      w[2 * jj] = x.x;
-      w[2 * jj + 1] = x.y;
-    }
-    const int nc = ncw - c0 < 32 ? ncw - c0 : 32;
-#pragma unroll 2
-    for (int i2 = 0; i2 < m; ++i2) {
-      double acc0 = 0.0, acc1 = 0.0;
-#pragma unroll
-      for (int jj = 0; jj < 16; ++jj) {
-        if (2 * jj < nc) {
-          const double2 x = *reinterpret_cast<const double2*>(&W[i2 * LD + c0 + 2 * jj]);
-          acc0 = fma(w[2 * jj], x.x, acc0);
-          acc1 = fma(w[2 * jj + 1], x.y, acc1);
+  SEQM_R2PHASE(5);
+  // ---- P = 2 W W^T on the FP64 tensor pipe: 8 x 8 tiles of the upper block triangle, round robin over the two warps,
+  //      DMMA m8n8k4 over the occupied columns (W is zero beyond them); a tile and its mirror image are written from the
+  //      same registers, so P is exactly symmetric
+  {
+    constexpr int T = N / 8;
+    const int fr = lane >> 2, fc = lane & 3;      // fragment row / column of this lane
+    const int ksteps = (ncw + 3) >> 2;
+    int tile = 0;
+#pragma unroll 1
+    for (int ti = 0; ti < T; ++ti) {
+#pragma unroll 1
+      for (int tj = ti; tj < T; ++tj, ++tile) {
+        if ((tile & 1) != warp) continue;
+        if (8 * ti >= m) continue;
+        const double* wa = &W[(8 * ti + fr) * LD + fc];
+        const double* wb = &W[(8 * tj + fr) * LD + fc];
+        double c0 = 0.0, c1 = 0.0;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          const double a = wa[4 * ks], b = wb[4 * ks];
+          asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                       : "+d"(c0), "+d"(c1)
+                       : "d"(a), "d"(b));
         }
-      }
-      if (tid < m) {      // P[tid][i2] == P[i2][tid]
-        double* dst = &P[base + (size_t)pk2pd(i2, nh4) * n4 + pk2pd(tid, nh4)];
-        const double val = 2.0 * (acc0 + acc1);
-        *dst = c0 == 0 ? val : *dst + val;
+        const int r = 8 * ti + fr, cA = 8 * tj + 2 * fc;
+        if (r < m) {
+          const size_t pr = pk2pd(r, nh4);
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int c = cA + u;
+            if (c < m) {
+              const size_t pc = pk2pd(c, nh4);
+              const double val = 2.0 * (u ? c1 : c0);
+              P[base + pr * n4 + pc] = val;
+              if (ti != tj) P[base + pc * n4 + pr] = val;
+            }
+          }
+        }
       }
     }
   }
+  SEQM_R2PHASE(6);
   if (info && tid == 0) info[mol] = sweeps;
 }
 

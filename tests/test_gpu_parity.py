@@ -121,7 +121,9 @@ def test_eigh_warp_kernel_sizes(mmax):
     i32 = torch.int32
     P, e, v = _ops.eigh_density(F.to(dev), nH.to(dev).to(i32), nh.to(dev).to(i32), nocc.to(dev).to(i32), S, mmax,
                                 want_eig=True)
-    assert float((e.cpu() - eref).abs().max()) < 2e-12
+    # eigenvalue = column norm - shift: its absolute error scales with the Gershgorin width of the matrix (~ 3 m here),
+    # 1e-14 of it at m = 63 (the stated parity bar for orbital energies is 1e-10)
+    assert float((e.cpu() - eref).abs().max()) < (2e-12 if mmax <= 32 else 5e-12)
     assert float((P.cpu() - Pref).abs().max()) < 1e-11
     assert float((P - P.transpose(1, 2)).abs().max()) == 0.0
     for b_, (a, h) in enumerate(shapes):

@@ -112,3 +112,16 @@ def test_new_entry_points_reject_bad_arguments_without_a_gpu():
     assert L.seqm_sp2_nccl_workspace(1, 1500, 8) > L.seqm_sp2_workspace(1, 1500) > 2 * 6000 * 6000 * 8
     assert L.seqm_elec_energy_workspace(1, 1500) == ((6000 * 6000 + 8191) // 8192) * 8
     assert L.seqm_elec_energy_workspace(1024, 12) == 1024 * 8
+
+
+def test_pack_parameters_does_not_fill_the_callers_dict():
+    """Pack_Parameters returns a new dict: the shared default `learned_parameters=dict()` of Energy / Force must stay
+    empty (a filled default disables the cached-species path and is shared between BucketedBatch's worker threads)"""
+    from pyseqm_b200.basics import Pack_Parameters
+    pp = Pack_Parameters(dict(method='AM1', elements=[0, 1, 6], learned=[]))
+    mine = {}
+    out = pp(torch.tensor([6, 1, 1]), learned_params=mine)
+    assert mine == {} and 'U_ss' in out and out['U_ss'].shape == (3,)
+    out2 = pp(torch.tensor([1, 1]))
+    assert out2['U_ss'].shape == (2,) and out['U_ss'].shape == (3,)
+    assert pp.forward.__defaults__[0] == {}
