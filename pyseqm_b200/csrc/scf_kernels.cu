@@ -114,33 +114,16 @@ pack_pair_kernel(int n4, int mld, int chunks, const uint8_t* __restrict__ active
   }
 }
 
-// Pulay store: FOCK[c] = F, FPPF[c] = triu(G - G^T) with G = F P.  mld > 0: G is the PACKED product (row stride
-// mld, molecule stride mld^2); rows / columns of the padded layout that hold no orbital give zero
+// Pulay store (padded ring): FOCK[c] = F, FPPF[c] = triu(G - G^T) with G = F P
 __global__ void __launch_bounds__(256)
 pulay_store_kernel(int n4, int chunks, int slot, const uint8_t* __restrict__ active, const double* __restrict__ F,
-                   const double* __restrict__ G, double* __restrict__ FOCK, double* __restrict__ FPPF, int mld,
-                   const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro) {
+                   const double* __restrict__ G, double* __restrict__ FOCK, double* __restrict__ FPPF) {
   const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
   if (active && !active[mol]) return;
   const size_t nn = (size_t)n4 * n4;
   const size_t src = (size_t)mol * nn;
   const size_t dst = ((size_t)mol * NFOCK + slot) * nn;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
-  if (mld > 0) {
-    const int nhv = nheavy[mol], nh4 = 4 * nhv, m = nh4 + nhydro[mol];
-    const double* Gm = G + (size_t)mol * mld * mld;
-    for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-      const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
-      FOCK[dst + idx] = F[src + idx];
-      // padded index -> packed index (or -1): heavy atoms keep theirs, hydrogen a keeps only its s orbital
-      const int qi = i < nh4 ? i : (((i & 3) == 0 && nhv + ((i - nh4) >> 2) < nhv + (m - nh4)) ? nh4 + ((i - nh4) >> 2) : -1);
-      const int qj = j < nh4 ? j : (((j & 3) == 0 && nhv + ((j - nh4) >> 2) < nhv + (m - nh4)) ? nh4 + ((j - nh4) >> 2) : -1);
-      double v = 0.0;
-      if (j >= i && qi >= 0 && qj >= 0) v = Gm[(size_t)qi * mld + qj] - Gm[(size_t)qj * mld + qi];
-      FPPF[dst + idx] = v;
-    }
-    return;
-  }
   for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
     const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
     FOCK[dst + idx] = F[src + idx];
@@ -151,12 +134,12 @@ pulay_store_kernel(int n4, int chunks, int slot, const uint8_t* __restrict__ act
 // partial sums of EMAT[c][s] = <FPPF[c], FPPF[s]> for s < cF: blockIdx.x = (molecule * NFOCK + s) * chunks + chunk
 // (items with s >= cF are not launched: grid covers s < cF through the index arithmetic below)
 __global__ void __launch_bounds__(256)
-pulay_emat_part_kernel(int n4, int chunks, int cF, int slot, const uint8_t* __restrict__ active,
+pulay_emat_part_kernel(size_t nn, int chunks, int cF, int slot, const uint8_t* __restrict__ active,
                        const double* __restrict__ FPPF, double* __restrict__ part) {
+  // nn = doubles per ring slot (n4^2, or mld^2 for the packed ring)
   const int item = blockIdx.x / chunks, chunk = blockIdx.x - item * chunks;
   const int mol = item / cF, s = item - mol * cF;
   if (active && !active[mol]) return;
-  const size_t nn = (size_t)n4 * n4;
   const double* a = FPPF + ((size_t)mol * NFOCK + slot) * nn;
   const double* b = FPPF + ((size_t)mol * NFOCK + s) * nn;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
@@ -243,6 +226,53 @@ pulay_extrapolate_kernel(int n4, int chunks, int cF, const uint8_t* __restrict__
     for (int s = 0; s < NFOCK; ++s)
       if (s < cF) acc += fo[(size_t)s * nn + idx] * coeff[s];
     out[idx] = acc;
+  }
+}
+
+// Packed Pulay ring (hydrogen-rich systems, see packed_comm in seqm_scf): a ring slot holds the PACKED matrices
+// (mld x mld instead of n4 x n4, 4-5 x fewer bytes for organic molecules): FOCK[c] = Fp, FPPF[c] = triu(Gp - Gp^T).
+// The packing keeps the order of the orbitals, so these are the non-zero elements of the padded matrices in the same
+// row-major order; only the grouping of the EMAT partial sums (chunks of the packed instead of the padded matrix) differs.
+__global__ void __launch_bounds__(256)
+pulay_store_packed_kernel(int mld, int chunks, int slot, const uint8_t* __restrict__ active, const double* __restrict__ Fp,
+                          const double* __restrict__ Gp, double* __restrict__ FOCK, double* __restrict__ FPPF) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  if (active && !active[mol]) return;
+  const size_t pk = (size_t)mld * mld;
+  const size_t src = (size_t)mol * pk, dst = ((size_t)mol * NFOCK + slot) * pk;
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < pk ? lo + RED_CHUNK : pk;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+    const int i = (int)(idx / mld), j = (int)(idx - (size_t)i * mld);
+    FOCK[dst + idx] = Fp[src + idx];
+    FPPF[dst + idx] = (j >= i) ? Gp[src + idx] - Gp[src + (size_t)j * mld + i] : 0.0;
+  }
+}
+
+// F = sum_s coeff_s FOCK[s] from the packed ring, written to the orbital positions of the padded F (the rest of F is
+// zero and stays zero: the Fock build writes orbital positions only)
+__global__ void __launch_bounds__(256)
+pulay_extrapolate_packed_kernel(int n4, int mld, int chunks, int cF, const uint8_t* __restrict__ active,
+                                const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro,
+                                const double* __restrict__ coeffs, const double* __restrict__ FOCK, double* __restrict__ F) {
+  const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
+  if (active && !active[mol]) return;
+  double coeff[NFOCK];
+#pragma unroll
+  for (int s = 0; s < NFOCK; ++s) coeff[s] = s < cF ? coeffs[(size_t)mol * NFOCK + s] : 0.0;
+  const int nh4 = 4 * nheavy[mol], m = nh4 + nhydro[mol];
+  const size_t pk = (size_t)mld * mld;
+  const double* fo = FOCK + (size_t)mol * NFOCK * pk;
+  double* out = F + (size_t)mol * n4 * n4;
+  const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < pk ? lo + RED_CHUNK : pk;
+  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+    const int i = (int)(idx / mld), j = (int)(idx - (size_t)i * mld);
+    if (i >= m || j >= m) continue;
+    double acc = 0.0;
+#pragma unroll
+    for (int s = 0; s < NFOCK; ++s)
+      if (s < cF) acc += fo[(size_t)s * pk + idx] * coeff[s];
+    const int pi = i < nh4 ? i : nh4 + 4 * (i - nh4), pj = j < nh4 ? j : nh4 + 4 * (j - nh4);
+    out[(size_t)pi * n4 + pj] = acc;
   }
 }
 
@@ -397,22 +427,22 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
       int r_ = launch_dgemm_batched(mld, mld, Fp, Pp, Gp, (long long)pk, B, nc, nullptr, st);
       if (r_) return r_;
       prof_mark("pulay_store", st);
-      pulay_store_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, slot, nc, F, Gp, wk.FOCK, wk.FPPF, mld,
-                                                                        nheavy, nhydro);
-      SEQM_CHECK_LAUNCH("pulay_store_kernel");
+      pulay_store_packed_kernel<<<(unsigned)((size_t)B * pchunks), 256, 0, st>>>(mld, pchunks, slot, nc, Fp, Gp, wk.FOCK, wk.FPPF);
+      SEQM_CHECK_LAUNCH("pulay_store_packed_kernel");
     } else {
       int r_ = launch_dgemm_batched(n4, n4, F, P, wk.G, (long long)nn, B, nc, nullptr, st);
       if (r_) return r_;
       prof_mark("pulay_store", st);
-      pulay_store_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, slot, nc, F, wk.G, wk.FOCK, wk.FPPF, 0,
-                                                                        nullptr, nullptr);
+      pulay_store_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, slot, nc, F, wk.G, wk.FOCK, wk.FPPF);
       SEQM_CHECK_LAUNCH("pulay_store_kernel");
     }
-    pulay_emat_part_kernel<<<(unsigned)((size_t)B * cF_ * chunks), 256, 0, st>>>(n4, chunks, cF_, slot, nc, wk.FPPF, wk.red);
+    const size_t rlen = packed_comm ? (size_t)mld * mld : nn;      // doubles per ring slot
+    const int rchunks = packed_comm ? red_chunks(rlen) : chunks;
+    pulay_emat_part_kernel<<<(unsigned)((size_t)B * cF_ * rchunks), 256, 0, st>>>(rlen, rchunks, cF_, slot, nc, wk.FPPF, wk.red);
     SEQM_CHECK_LAUNCH("pulay_emat_part_kernel");
     pulay_emat_index_kernel<<<cdiv((long long)B * cF_, 256), 256, 0, st>>>(B * cF_, cF_, slot, wk.emat_index);
     SEQM_CHECK_LAUNCH("pulay_emat_index_kernel");
-    return launch_chunk_sum(B * cF_, chunks, nc, cF_, wk.red, wk.EMAT, wk.emat_index, st);
+    return launch_chunk_sum(B * cF_, rchunks, nc, cF_, wk.red, wk.EMAT, wk.emat_index, st);
   };
   auto refock_and_finish = [&](bool store, int& counter, int& cF) -> int {
     int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, wk.red, st);
@@ -492,7 +522,13 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
       while (left > 0) {
         prof_mark("pulay_extrapolate", st);
         pulay_coeff_kernel<<<cdiv(B, 128), 128, 0, st>>>(B, counter, cF, nc, wk.EMAT, wk.coeff);
-        pulay_extrapolate_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, cF, nc, wk.coeff, wk.FOCK, F);
+        if (packed_comm) {
+          const int pchunks = red_chunks((size_t)mld * mld);
+          pulay_extrapolate_packed_kernel<<<(unsigned)((size_t)B * pchunks), 256, 0, st>>>(n4, mld, pchunks, cF, nc, nheavy, nhydro,
+                                                                                        wk.coeff, wk.FOCK, F);
+        } else {
+          pulay_extrapolate_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, cF, nc, wk.coeff, wk.FOCK, F);
+        }
         g_launches += 2;
         { cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { set_error(std::string("pulay_extrapolate_kernel: ") + cudaGetErrorString(e_)); return SEQM_ECUDA; } }
         SEQM_TRY(density(P));
