@@ -132,6 +132,42 @@ def test_eigh_warp_kernel_sizes(mmax):
         assert float((C.T @ C - torch.eye(m)).abs().max()) < 1e-13
 
 
+@pytest.mark.parametrize('name', ['benzene8_AM1_eigh_c2', 'mixed12_MNDO_eigh_c2', 'small_PM3_eigh_c2'])
+def test_ring_jacobi_against_two_sided_jacobi(name):
+    """two independent eigensolvers on the reference's Fock matrices: the one-sided ring Jacobi (default) and the
+    two-sided odd-even warp Jacobi / shared-memory Jacobi kept behind seqm_eigh_warp_variant(0) give the same density and
+    orbital energies; the same through a whole SCF (one-launch kernel with either solver)"""
+    from pyseqm_b200 import _lib, _ops
+    from pyseqm_b200.basics import Force
+    from pyseqm_b200.seqm_functions.constants import Constants
+    dev = _dev()
+    g = _load(name)
+    i32 = torch.int32
+    nH, nh, nocc = (torch.as_tensor(g[k]).to(dev).to(i32) for k in ('nHeavy', 'nHydro', 'nocc'))
+    F = _t(g['F'], dev)
+    molsize = F.shape[-1] // 4
+    mmax = int((4 * nH + nh).max())
+    const = Constants().to(dev)
+    res = {}
+    try:
+        for variant in (1, 0):
+            _lib.lib().seqm_eigh_warp_variant(variant)
+            P, e, v = _ops.eigh_density(F, nH, nh, nocc, molsize, mmax, want_eig=True)
+            out = Force(_params(g)).to(dev)(const, _t(g["coords"], dev), _t(g["species"], dev))
+            torch.cuda.synchronize()
+            res[variant] = (P.clone(), e.clone(), out[2].detach().clone(), out[0].clone())
+    finally:
+        _lib.lib().seqm_eigh_warp_variant(1)
+    keep = np.ones(F.shape[0], dtype=bool)
+    keep[NOISE_DIIS.get(name, [])] = False
+    # each solver is within 1e-9 of the reference's density (test_hcore_fock_density_ops); exactly degenerate orbitals
+    # (methane, ammonia in mixed12) are where they differ most
+    assert float((res[1][0] - res[0][0]).abs().cpu()[keep].max()) < 2e-9
+    assert float((res[1][1] - res[0][1]).abs().max()) < 1e-10
+    assert float((res[1][2] - res[0][2]).abs().max()) < 1e-7
+    assert float((res[1][3] - res[0][3]).abs().max()) < 1e-6
+
+
 @pytest.mark.parametrize('name', golden_names())
 def test_hcore_fock_density_ops(name):
     """op-level parity on the reference's own intermediate tensors"""
