@@ -12,7 +12,8 @@ int launch_dgemm_batched(int n, int ld, const double* A, const double* B, double
 
 int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const double* M, const double* g_ss,
                 const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
-                const uint8_t* active, double* F, double* Eelec, double* pairvec, double* scratch, cudaStream_t st);
+                const uint8_t* active, double* F, double* Eelec, double* pairvec, double* scratch, cudaStream_t st,
+                const int32_t* nheavy = nullptr, const int32_t* nhydro = nullptr);      // given: energy over orbital rows only
 // chunked per-molecule reductions for large molecules (fock_kernels.cu): RED_CHUNK elements per CTA, partial sums in
 // scratch [items][chunks], summed in a fixed order
 constexpr int RED_CHUNK = 8192;
@@ -20,7 +21,8 @@ int red_chunks(size_t nn);
 int launch_chunk_sum(int items, int chunks, const uint8_t* active, int items_per_mol, const double* part, double* out,
                      const int32_t* out_index, cudaStream_t st);
 int launch_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
-                       const double* D, int xl, const uint8_t* active, double* E, double* scratch, cudaStream_t st);
+                       const double* D, int xl, const uint8_t* active, double* E, double* scratch, cudaStream_t st,
+                       const int32_t* nheavy = nullptr, const int32_t* nhydro = nullptr);
 
 int launch_eigh_density(int64_t nmol, int64_t molsize, int mmax, const double* F, const int32_t* nheavy,
                         const int32_t* nhydro, const int32_t* nocc, const uint8_t* active, double* P,

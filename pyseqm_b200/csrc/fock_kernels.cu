@@ -201,16 +201,23 @@ elec_energy_kernel(int S, const double* __restrict__ P, const double* __restrict
 __global__ void __launch_bounds__(256)
 elec_energy_part_kernel(int S, int chunks, const double* __restrict__ P, const double* __restrict__ F,
                         const double* __restrict__ M, const double* __restrict__ D, int xl,
-                        const uint8_t* __restrict__ active, double* __restrict__ part) {
+                        const uint8_t* __restrict__ active, double* __restrict__ part,
+                        const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro) {
   const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
   if (active && !active[mol]) return;
   const int n4 = 4 * S;
-  const size_t nn = (size_t)n4 * n4, base = (size_t)mol * nn;
+  // nheavy / nhydro given: only the rows that hold an orbital are read (the others are zero in P): for hydrogen-rich
+  // molecules that is half of the padded matrix or less
+  const int nh4 = nheavy ? 4 * nheavy[mol] : n4;
+  const int mrow = nheavy ? nh4 + nhydro[mol] : n4;
+  const size_t nn = (size_t)mrow * n4, base = (size_t)mol * n4 * n4;
   const size_t lo = (size_t)chunk * RED_CHUNK;
   const size_t hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   double acc = 0.0;
-  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-    const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
+  for (size_t idx0 = lo + threadIdx.x; idx0 < hi; idx0 += blockDim.x) {
+    const int ip = (int)(idx0 / n4), j = (int)(idx0 - (size_t)ip * n4);
+    const int i = ip < nh4 ? ip : nh4 + 4 * (ip - nh4);
+    const size_t idx = (size_t)i * n4 + j;
     const int ai = i >> 2, mu = i & 3, aj = j >> 2, nu = j & 3;
     double h;
     if (ai < aj || (ai == aj && mu <= nu)) h = M[(((size_t)mol * S + ai) * S + aj) * 16 + mu * 4 + nu];
@@ -261,7 +268,8 @@ int launch_chunk_sum(int items, int chunks, const uint8_t* active, int items_per
 }
 
 int launch_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
-                       const double* D, int xl, const uint8_t* active, double* E, double* scratch, cudaStream_t st) {
+                       const double* D, int xl, const uint8_t* active, double* E, double* scratch, cudaStream_t st,
+                       const int32_t* nheavy, const int32_t* nhydro) {
   const size_t nn = (size_t)16 * molsize * molsize;
   const int chunks = red_chunks(nn);
   if (!scratch || chunks == 1) {
@@ -270,14 +278,16 @@ int launch_elec_energy(int64_t nmol, int64_t molsize, const double* P, const dou
     return SEQM_OK;
   }
   SEQM_REQUIRE((long long)nmol * chunks < (1LL << 31), "elec_energy: too many chunks");
-  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, scratch);
+  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, scratch,
+                                                                   nheavy, nhydro);
   SEQM_CHECK_LAUNCH("elec_energy_part_kernel");
   return launch_chunk_sum((int)nmol, chunks, active, 1, scratch, E, nullptr, st);
 }
 
 int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const double* M, const double* g_ss,
                 const double* g_pp, const double* g_sp, const double* g_p2, const double* h_sp,
-                const uint8_t* active, double* F, double* Eelec, double* pairvec, double* scratch, cudaStream_t st) {
+                const uint8_t* active, double* F, double* Eelec, double* pairvec, double* scratch, cudaStream_t st,
+                const int32_t* nheavy, const int32_t* nhydro) {
   prof_mark("fock_pair", st);
   if (t.ncls[2] > 0) {
     fock_pair_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, w.wXX, P, M, active, F, pairvec);
@@ -298,7 +308,7 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
   }
   prof_mark("elec_energy", st);
   if (Eelec && t.nmol > 0) {
-    const int rc_ = launch_elec_energy(t.nmol, t.molsize, P, F, M, nullptr, 0, active, Eelec, scratch, st);
+    const int rc_ = launch_elec_energy(t.nmol, t.molsize, P, F, M, nullptr, 0, active, Eelec, scratch, st, nheavy, nhydro);
     if (rc_) return rc_;
   }
   prof_mark("end", st);
@@ -375,7 +385,7 @@ int seqm_elec_energy_noalloc(int64_t nmol, int64_t molsize, const double* P, con
   cudaStream_t st = (cudaStream_t)stream;
   prof_mark("elec_energy", st);
   // always the chunked pair of kernels (also when a molecule is a single chunk): partial sums -> fixed-order sum
-  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, part);
+  elec_energy_part_kernel<<<(unsigned)(nmol * chunks), 256, 0, st>>>((int)molsize, chunks, P, F, M, D, xl, active, part, nullptr, nullptr);
   SEQM_CHECK_LAUNCH("elec_energy_part_kernel");
   const int rc2 = launch_chunk_sum((int)nmol, chunks, active, 1, part, E, nullptr, st);
   prof_mark("end", st);

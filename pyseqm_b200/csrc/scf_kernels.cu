@@ -24,13 +24,16 @@ enum MixMode { MIX_DIRECT = 0, MIX_CONST = 1, MIX_ADAPTIVE = 2, MIX_TAKE = 3 };
 // RED_CHUNK matrix elements, one CTA per (molecule, chunk): blockIdx.x = molecule * chunks + chunk.
 __global__ void __launch_bounds__(256)
 mix_fac_kernel(int n4, const uint8_t* __restrict__ active, const double* __restrict__ Pnew,
-               const double* __restrict__ P, const double* __restrict__ Pold, double* __restrict__ fac_out) {
+               const double* __restrict__ P, const double* __restrict__ Pold, double* __restrict__ fac_out,
+               const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro) {
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const size_t base = (size_t)mol * n4 * n4;
+  const int nh4 = 4 * nheavy[mol], m = nh4 + nhydro[mol];      // the diagonal elements that belong to an orbital (the others are zero)
   __shared__ double red[2][8];
   double num = 0.0, den = 0.0;
-  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+  for (int ip = threadIdx.x; ip < m; ip += blockDim.x) {
+    const int i = ip < nh4 ? ip : nh4 + 4 * (ip - nh4);
     const size_t d = base + (size_t)i * n4 + i;
     const double dn = Pnew[d], dc = P[d], dold = Pold[d];
     num += (dn - dc) * (dn - dc);
@@ -54,13 +57,17 @@ mix_fac_kernel(int n4, const uint8_t* __restrict__ active, const double* __restr
 __global__ void __launch_bounds__(256)
 mix_kernel(int n4, int chunks, int mode, double alpha, const uint8_t* __restrict__ active,
            const double* __restrict__ Pnew, double* __restrict__ P, double* __restrict__ Pold,
-           const double* __restrict__ facs) {
+           const double* __restrict__ facs, const int32_t* __restrict__ nheavy, const int32_t* __restrict__ nhydro) {
   const int mol = blockIdx.x / chunks, chunk = blockIdx.x - mol * chunks;
   if (active && !active[mol]) return;
-  const size_t nn = (size_t)n4 * n4, base = (size_t)mol * nn;
+  // only the rows that hold an orbital: the density step writes nothing else, and nothing reads the other rows of Pold
+  const int nh4 = 4 * nheavy[mol], m = nh4 + nhydro[mol];
+  const size_t nn = (size_t)m * n4, base = (size_t)mol * n4 * n4;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   const double fac = mode == MIX_ADAPTIVE ? facs[mol] : 0.0;
-  for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
+  for (size_t idx0 = lo + threadIdx.x; idx0 < hi; idx0 += blockDim.x) {
+    const int ip = (int)(idx0 / n4);
+    const size_t idx = (size_t)(ip < nh4 ? ip : nh4 + 4 * (ip - nh4)) * n4 + (idx0 - (size_t)ip * n4);
     const double pn = Pnew[base + idx];
     const double pc = P[base + idx];
     if (mode == MIX_DIRECT) { Pold[base + idx] = pc; P[base + idx] = pn; }
@@ -389,7 +396,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   init_flags_kernel<<<cdiv(B, 256), 256, 0, st>>>(B, nc, wk.err, niter, wk.EMAT);
   SEQM_CHECK_LAUNCH("init_flags_kernel");
   // F = fock(P), Eelec
-  rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, wk.red, st);
+  rc = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nullptr, F, Eelec, pairvec, wk.red, st, nheavy, nhydro);
   if (rc) return rc;
 
   unsigned long long* hstat = host_status_slot();
@@ -445,7 +452,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
     return launch_chunk_sum(B * cF_, rchunks, nc, cF_, wk.red, wk.EMAT, wk.emat_index, st);
   };
   auto refock_and_finish = [&](bool store, int& counter, int& cF) -> int {
-    int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, wk.red, st);
+    int r = launch_fock(t, w, P, M, g_ss, g_pp, g_sp, g_p2, h_sp, nc, F, wk.Enew, pairvec, wk.red, st, nheavy, nhydro);
     if (r) return r;
     if (store) {
       cF = cF < NFOCK ? cF + 1 : NFOCK;
@@ -473,10 +480,11 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   auto mix = [&](int mode) -> int {
     prof_mark("mix", st);
     if (mode == MIX_ADAPTIVE) {
-      mix_fac_kernel<<<B, 256, 0, st>>>(n4, nc, wk.Pnew, P, wk.Pold, wk.fac);
+      mix_fac_kernel<<<B, 256, 0, st>>>(n4, nc, wk.Pnew, P, wk.Pold, wk.fac, nheavy, nhydro);
       SEQM_CHECK_LAUNCH("mix_fac_kernel");
     }
-    mix_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold, wk.fac);
+    mix_kernel<<<(unsigned)((size_t)B * chunks), 256, 0, st>>>(n4, chunks, mode, opt->alpha, nc, wk.Pnew, P, wk.Pold, wk.fac,
+                                                              nheavy, nhydro);
     SEQM_CHECK_LAUNCH("mix_kernel");
     return SEQM_OK;
   };
