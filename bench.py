@@ -915,8 +915,8 @@ def run_organics(ctx):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=10)
-    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--steps', type=int, default=100)
+    ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200')
     ap.add_argument('--workload', default='all', choices=['all', 'benzene', 'c60xl', 'water', 'organics'])
     args = ap.parse_args()
