@@ -227,7 +227,7 @@ eigh_cluster_kernel(int S, const double* __restrict__ F, const int32_t* __restri
     __syncwarp();
     // The warp Jacobi leaves the eigenvectors in an arbitrary column order.  Block Jacobi only converges if the
     // transformation stays close to the identity when the pair is already nearly orthogonal (bounded-cosine condition:
-    // an arbitrary column order just shuffles columns between the two blocks - tools/proto/block_hestenes.py stagnates
+    // an arbitrary column order just shuffles columns between the two blocks - tests/dev/proto/block_hestenes.py stagnates
     // at 1e-2 without this).  Greedy assignment: output column k takes the unassigned eigenvector with the largest
     // |Q[k][c]|; the reordered matrix goes to S0 (row stride LDG), where update_phase reads it.
     bool taken = lane >= N;

@@ -104,7 +104,7 @@ template <int H, int R> struct RingCols {
     const float tf = (df >= 0.0f ? bf : -bf) * rcp_approx(fmaf(h2, rsqrt_approx(h2), fabsf(df)));
     // columns already orthogonal to rounding are left alone: inside an exactly degenerate cluster gamma and the norm
     // difference are both noise, the angle would be arbitrary, and such a rotation re-mixes the cluster's couplings to
-    // the other columns (the sweep then no longer converges quadratically; tools/proto/onesided_ring.py)
+    // the other columns (the sweep then no longer converges quadratically; tests/dev/proto/onesided_ring.py)
     // (a small angle is harmless and is applied: it is what separates close but distinct eigenvalues)
     const double g2 = gam * gam;
     const bool noise = g2 <= (RING_COS_MIN * RING_COS_MIN) * (ap * aq) && fabsf(tf) > RING_T_NOISE;

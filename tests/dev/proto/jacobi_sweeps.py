@@ -3,7 +3,7 @@ iteration's eigenvectors, stop rule: one last sweep once off^2 <= tol tot^2): sw
 import os, sys
 import numpy as np
 import torch
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 import seqm_oracle as orc
 from pyseqm_b200 import synth

@@ -6,7 +6,7 @@ of an oracle SCF run.  Test infrastructure only (uses oracle/)."""
 import os, sys
 import numpy as np
 import torch
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 torch.set_default_dtype(torch.float64)
 import seqm_oracle as orc
