@@ -42,7 +42,11 @@ template <int N> struct Ring {
   static constexpr int R = (N <= 8) ? 8 : ((N <= 16) ? 4 : 2);      // lanes per processor
   static constexpr int K = 32 / R;                                  // processors, 2K column slots
   static constexpr int H = N / R;                                   // rows per lane
-  static_assert(N % R == 0 && 2 * K >= N, "row split / column slots");
+  // processors that take part in the schedule: all K.  (N / 2 = 10, 12, 14 processors for 20, 24, 28 columns give 2 KA
+  // instead of 31 rounds, but their last KA / 2 rounds carry two extra column exchanges each: measured no faster at
+  // H <= 14 rows per lane; the two-warp kernel with H >= 20 does use the shorter schedules.)
+  static constexpr int KA = K;
+  static_assert(N % R == 0 && 2 * K >= N && 2 * KA >= N, "row split / column slots");
 };
 
 __device__ __forceinline__ float rsqrt_approx(float x) {
@@ -138,37 +142,65 @@ template <int H, int R> struct RingCols {
     SEQM_TICK(5);
   }
 
-  // the two halves of a group of processors exchange one column inside the warp: all P's to the first half, all Q's to
-  // the second; xm = lane distance of the partner processor
-  __device__ __forceinline__ void exchange(bool first, int xm) {
+  // two processors exchange one column inside the warp: the `first` one gives its Q and takes the partner's P into its
+  // Q slot, the other gives its P and takes the partner's Q into its P slot; plane = the partner's lane with the same
+  // row part (the own lane: nothing changes)
+  __device__ __forceinline__ void exchange(bool first, int plane) {
 #pragma unroll
     for (int i = 0; i < H; ++i) {
-      const double got = __shfl_xor_sync(FULL, first ? gq[i] : gp[i], xm);
+      const double got = __shfl_sync(FULL, first ? gq[i] : gp[i], plane);
       gq[i] = first ? got : gq[i];
       gp[i] = first ? gp[i] : got;
     }
-    const double g_d = __shfl_xor_sync(FULL, first ? dq : dp, xm);
-    const double g_i = __shfl_xor_sync(FULL, first ? idq : idp, xm);
-    const double g_a = __shfl_xor_sync(FULL, first ? aq : ap, xm);
+    const double g_d = __shfl_sync(FULL, first ? dq : dp, plane);
+    const double g_i = __shfl_sync(FULL, first ? idq : idp, plane);
+    const double g_a = __shfl_sync(FULL, first ? aq : ap, plane);
     dq = first ? g_d : dq; idq = first ? g_i : idq; aq = first ? g_a : aq;
     dp = first ? dp : g_d; idp = first ? idp : g_i; ap = first ? ap : g_a;
   }
 
-  // Kg rounds of a ring of Kg processors (P stays, Q moves on by one processor after every round but the last)
-  __device__ __forceinline__ void ring(int Kg, int kw, int h, int lane) {
-    const int src = (((kw & ~(Kg - 1)) | ((kw - 1) & (Kg - 1))) * R) + h;      // previous processor of the group, same row part
+  // g rounds of a ring of the g processors base .. base + g - 1 (P stays, Q moves on by one processor after every round
+  // but the last); idle: a processor outside the schedule (it holds empty columns and shuffles with itself)
+  __device__ __forceinline__ void ring(int g, int base, int kw, int h, int lane, bool idle) {
+    const int src = idle ? lane : (base + (kw - base + g - 1) % g) * R + h;      // previous processor of the group, same row part
 #pragma unroll 1
-    for (int r = 0; r < Kg; ++r) rotate(r + 1 < Kg ? src : lane);
+    for (int r = 0; r < g; ++r) rotate(r + 1 < g ? src : lane);
   }
 
-  // all pairs among the 2 * K0 columns held by the K0 processors of one warp (kw = processor index inside the warp):
-  // phases of group size K0, K0/2, .., 1.  ONE copy of the round in the instruction stream (the one-launch SCF kernel
-  // around it is large and its warps run different phases: unrolled phases showed as no_instruction stalls)
+  // All pairs among the 2 K0 columns held by the processors 0 .. K0 - 1 of one warp (kw = processor index inside the
+  // warp; processors >= K0 idle).  Group of g processors: ring(g) lets every P meet every Q of the group; g even: the
+  // halves exchange (P's to the first half, Q's to the second) and each half is a group of g / 2; g odd (3, 5, 7 - the
+  // end of K0 = 12, 10, 14): round robin of the g P's and the g Q's in g more rounds - in round r processor i swaps one
+  // column with processor (2r - i) mod g, rotates, and swaps back (processor r rotates its own pair once more).
+  // Rounds: 2 K0 - 1 for K0 = 2^k, 2 K0 for K0 = 10, 12, 14 (tests/dev/proto/ring_schedule.py checks the coverage).
+  // ONE copy of the round in the instruction stream (the one-launch SCF kernel around it is large and its warps run
+  // different phases: unrolled phases showed as no_instruction stalls).
   __device__ __forceinline__ void phases(int K0, int kw, int h, int lane) {
+    const bool idle = kw >= K0;
+    int g = K0, base = 0;
 #pragma unroll 1
-    for (int Kg = K0; Kg >= 1; Kg >>= 1) {
-      ring(Kg, kw, h, lane);
-      if (Kg > 1) exchange((kw & (Kg >> 1)) == 0, (Kg >> 1) * R);
+    for (;;) {
+      ring(g, base, kw, h, lane, idle);
+      if (g == 1) break;
+      if ((g & 1) == 0) {
+        const int half = g >> 1;
+        const bool first = kw - base < half;
+        exchange(first, idle ? lane : (first ? kw + half : kw - half) * R + h);
+        if (!first) base += half;
+        g = half;
+      } else {
+        const int hh = (g - 1) >> 1, i = kw - base;
+#pragma unroll 1
+        for (int r = 0; r < g; ++r) {
+          const int d = (i - r + g) % g;      // 0: the bye
+          const bool first = d > hh;
+          const int plane = (idle || d == 0) ? lane : (base + (2 * r - i + 2 * g) % g) * R + h;
+          exchange(first, plane);
+          rotate(lane);
+          exchange(first, plane);
+        }
+        break;
+      }
     }
   }
 };
@@ -270,7 +302,7 @@ __device__ __forceinline__ int ring_eigh_density(double* __restrict__ S0, double
     C.renorm();
     C.off = 0.0;
     const double tot = C.ap * C.ap + C.aq * C.aq;
-    C.phases(K, k, h, lane);
+    C.phases(Ring<N>::KA, k, h, lane);
     ++sweeps;
     // every lane of a processor carries the same off / tot
     const double off2 = 2.0 * warp_sum(C.off), tot2 = warp_sum(tot);

@@ -1,12 +1,12 @@
 // K3a for packed sizes 32 < m <= 64: the one-sided ring Jacobi of eigh_ring.cuh on TWO warps per molecule.
-// 64 column slots on 32 processors of 2 lanes (a lane holds H = N / 2 rows of its processor's columns P and Q in
-// registers, 2H <= 64 doubles); processors 0..15 live in warp 0, 16..31 in warp 1.  A sweep of 63 rounds:
-//   1. ring of 16 inside each warp (16 rounds): every P of a warp meets every Q of that warp;
-//   2. the warps swap their Q columns through shared memory (ONE block barrier pair), ring of 16 again: now every P
-//      has met all 32 Q's;
+// N = 4 K0 column slots on 2 K0 processors of 2 lanes (a lane holds H = N / 2 rows of its processor's columns P and Q
+// in registers, 2H <= 64 doubles), K0 = 10, 12, 14 or 16 processors per warp.  A sweep of 4 K0 (K0 = 16: 63) rounds:
+//   1. ring of K0 inside each warp (K0 rounds): every P of a warp meets every Q of that warp;
+//   2. the warps swap their Q columns through shared memory (ONE block barrier pair), ring of K0 again: now every P
+//      has met all 2 K0 Q's;
 //   3. all P's go to warp 0, all Q's to warp 1 (second and last exchange through shared memory);
-//   4. each warp finishes its own 32 columns with the recursive phases 16, 8, 4, 2, 1 (31 rounds) without any
-//      synchronisation between the warps.
+//   4. each warp finishes its own 2 K0 columns with the recursive phases of RingCols::phases (K0, K0 / 2, ..) without
+//      any synchronisation between the warps.
 // So the warps meet twice per sweep (plus once for the convergence sums); everything else is registers and shuffles.
 // The shared-memory (CTA) Jacobi this replaces moved ~6 m^2 doubles through shared memory per round behind two block
 // barriers: 73 % of the config-4 sweep at 13 % FP64-pipe utilisation (profiles/r01q_grad_eigh_ncu.txt).
@@ -33,7 +33,8 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
                   double* __restrict__ v_out, int32_t* __restrict__ info, double* __restrict__ Vstore, int warm,
                   double tol) {
   constexpr int H = N / 2, R = 2, LD = N + 2;
-  static_assert(N % 2 == 0 && N > 32 && N <= 64, "packed size handled by two warps");
+  constexpr int K0 = N / 4;      // processors per warp that take part (10, 12, 14, 16): 4 K0 = N column slots
+  static_assert(N % 8 == 0 && N > 32 && N <= 64, "packed size handled by two warps");
   extern __shared__ __align__(16) double sm[];
   double* S0 = sm;                       // [N][LD]
   double* red = sm + N * LD;             // [8] block reductions
@@ -46,9 +47,11 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   const int n4 = 4 * S;
   const size_t base = (size_t)mol * n4 * n4;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int k = tid >> 1, kw = k & 15, h = tid & 1;      // processor, processor inside the warp, row part
+  const int kw = lane >> 1, h = tid & 1;      // processor inside the warp, row part
+  const bool idle = kw >= K0;
   const int row0 = h * H;
-  const int sP = 2 * k;
+  // column slot of P (Q: sP + 1); the idle processors take the slots beyond the 4 K0 = N columns
+  const int sP = idle ? 2 * (2 * K0 + warp * (16 - K0) + (kw - K0)) : 2 * (warp * K0 + kw);
   double* Vg = Vstore ? Vstore + (size_t)mol * N * RING2_SLOTS : nullptr;
 
   SEQM_R2PHASE(-1);
@@ -156,7 +159,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
     C.off = 0.0;
     const double tot = C.ap * C.ap + C.aq * C.aq;
     // 1. every P of a warp meets every Q of that warp
-    C.ring(16, kw, h, lane);
+    C.ring(K0, 0, kw, h, lane, idle);
     // 2. the warps swap their Q columns; ring again
 #pragma unroll
     for (int i = 0; i < H; ++i) X[i * 64 + tid] = gq[i];
@@ -166,7 +169,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
     for (int i = 0; i < H; ++i) gq[i] = X[i * 64 + (tid ^ 32)];
     C.dq = X[H * 64 + (tid ^ 32)]; C.idq = X[(H + 1) * 64 + (tid ^ 32)]; C.aq = X[(H + 2) * 64 + (tid ^ 32)];
     __syncthreads();
-    C.ring(16, kw, h, lane);
+    C.ring(K0, 0, kw, h, lane, idle);
     // 3. all P's to warp 0 (into its Q slots), all Q's to warp 1 (into its P slots)
     if (warp == 0) {
 #pragma unroll
@@ -188,7 +191,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
       C.dp = X[H * 64 + (tid ^ 32)]; C.idp = X[(H + 1) * 64 + (tid ^ 32)]; C.ap = X[(H + 2) * 64 + (tid ^ 32)];
     }
     // 4. each warp finishes its own 32 columns
-    C.phases(16, kw, h, lane);
+    C.phases(K0, kw, h, lane);
     ++sweeps;
     // every lane of a processor carries the same off / tot
     const double offw = warp_sum(C.off), totw = warp_sum(tot);
