@@ -38,6 +38,7 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   extern __shared__ __align__(16) double sm[];
   double* S0 = sm;                       // [N][LD]
   double* red = sm + N * LD;             // [8] block reductions
+  double* ev = red + 8;                  // [64] eigenvalues by slot; behind it [N][8] + [N][8] staging of the warm start
   const int mol = blockIdx.x;
   if (active && !active[mol]) return;
   const int nh4 = 4 * nheavy[mol];
@@ -108,28 +109,73 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
   RingCols<H, R> C;
   double (&gp)[H] = C.gp, (&gq)[H] = C.gq;
   if (warm && Vg) {
+    // On the FP64 tensor pipe (DMMA m8n8k4), eight column slots at a time: both warps multiply the N x N matrix
+    // (shared memory, sigma added to its diagonal) by the N x 8 chunk of V0 (staged in shared memory, the next chunk
+    // prefetched into registers), the N x 8 result goes through a staging buffer to the eight lanes that own those
+    // slots.  (As N FMAs per element on the FP64 pipe this product cost 38 k cycles of a ~250 k cycle solve.)
+    double* vch = ev + 64;            // [N][8] chunk of V0
+    double* stage = vch + N * 8;      // [N][8] chunk of G
+    if (tid < m) S0[tid * LD + tid] += sigma;
 #pragma unroll
-    for (int i = 0; i < H; ++i) {
-      const double2 x = *reinterpret_cast<const double2*>(&Vg[(row0 + i) * RING2_SLOTS + sP]);
-      gp[i] = sigma * x.x;
-      gq[i] = sigma * x.y;
+    for (int i = 0; i < H; ++i) { gp[i] = 0.0; gq[i] = 0.0; }
+    constexpr int NCH = N / 8, PER = (N * 8 + 63) / 64;      // chunks; V0 elements per thread and chunk
+    const int fr = lane >> 2, fc = lane & 3;
+    double pre[PER];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int e = tid + 64 * u;      // element (row e / 8, column e % 8) of the chunk
+      pre[u] = e < N * 8 ? Vg[(e >> 3) * RING2_SLOTS + (e & 7)] : 0.0;
     }
-    double2 va = *reinterpret_cast<const double2*>(&Vg[0 * RING2_SLOTS + sP]);
-    double2 vb = *reinterpret_cast<const double2*>(&Vg[1 * RING2_SLOTS + sP]);
 #pragma unroll 1
-    for (int jj = 0; jj < N / 2; ++jj) {
-      const double2 ca = va, cb = vb;
-      if (jj + 1 < N / 2) {      // next two rows of V0 on their way while this pair is used
-        va = *reinterpret_cast<const double2*>(&Vg[(2 * jj + 2) * RING2_SLOTS + sP]);
-        vb = *reinterpret_cast<const double2*>(&Vg[(2 * jj + 3) * RING2_SLOTS + sP]);
-      }
+    for (int tj = 0; tj < NCH; ++tj) {
 #pragma unroll
-      for (int i = 0; i < H; ++i) {
-        const double2 a2 = *reinterpret_cast<const double2*>(&S0[(row0 + i) * LD + 2 * jj]);
-        gp[i] = fma(a2.x, ca.x, gp[i]);
-        gq[i] = fma(a2.x, ca.y, gq[i]);
-        gp[i] = fma(a2.y, cb.x, gp[i]);
-        gq[i] = fma(a2.y, cb.y, gq[i]);
+      for (int u = 0; u < PER; ++u) {
+        const int e = tid + 64 * u;
+        if (e < N * 8) vch[e] = pre[u];
+      }
+      if (tj + 1 < NCH) {
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+          const int e = tid + 64 * u;
+          pre[u] = e < N * 8 ? Vg[(e >> 3) * RING2_SLOTS + 8 * (tj + 1) + (e & 7)] : 0.0;
+        }
+      }
+      __syncthreads();      // chunk of V0 (and, first time, the shifted diagonal) visible; stage free
+      {
+        // the row tiles warp, warp + 2, .. of this warp side by side: independent accumulators hide the DMMA latency
+        constexpr int TPW = (NCH + 1) / 2;
+        double c0[TPW], c1[TPW];
+#pragma unroll
+        for (int q = 0; q < TPW; ++q) { c0[q] = 0.0; c1[q] = 0.0; }
+#pragma unroll 2
+        for (int ks = 0; ks < N / 4; ++ks) {
+          const double b = vch[(4 * ks + fc) * 8 + fr];
+#pragma unroll
+          for (int q = 0; q < TPW; ++q) {
+            const int ti = warp + 2 * q;
+            if (ti < NCH) {      // warp uniform
+              const double a = S0[(8 * ti + fr) * LD + fc + 4 * ks];
+              asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                           : "+d"(c0[q]), "+d"(c1[q])
+                           : "d"(a), "d"(b));
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < TPW; ++q) {
+          const int ti = warp + 2 * q;
+          if (ti < NCH) *reinterpret_cast<double2*>(&stage[(8 * ti + fr) * 8 + 2 * fc]) = make_double2(c0[q], c1[q]);
+        }
+      }
+      __syncthreads();
+      if ((sP >> 3) == tj) {
+        const int col = sP & 7;
+#pragma unroll
+        for (int i = 0; i < H; ++i) {
+          const double2 x = *reinterpret_cast<const double2*>(&stage[(row0 + i) * 8 + col]);
+          gp[i] = x.x;
+          gq[i] = x.y;
+        }
       }
     }
 #pragma unroll
@@ -206,7 +252,6 @@ eigh_ring2_kernel(int S, const double* __restrict__ F, const int32_t* __restrict
 
   SEQM_R2PHASE(3);
   // ---- eigenvalues and ranking: slot tid = column P (h = 0) or Q (h = 1) of processor k
-  double* ev = red + 8;      // [64]
   const double amine = h ? aq : ap;
   const bool real = amine > 0.0;
   const double e = real ? sqrt(amine) - sigma : 0.0;
@@ -299,7 +344,7 @@ static int launch_ring2_n(int64_t nmol, int S, const double* F, const int32_t* n
                           int32_t* info, double* Vstore, int warm, double tol, cudaStream_t st) {
   constexpr int H = N / 2, LD = N + 2;
   constexpr size_t cells = (size_t)N * LD > (size_t)64 * (H + 3) ? (size_t)N * LD : (size_t)64 * (H + 3);
-  constexpr size_t smem = (cells + 8 + 64) * sizeof(double);
+  constexpr size_t smem = (cells + 8 + 64 + 2 * N * 8) * sizeof(double);
   static_assert(smem <= 48 * 1024, "fits the default dynamic shared memory limit");
   eigh_ring2_kernel<N><<<(unsigned)nmol, 64, smem, st>>>(S, F, nheavy, nhydro, nocc, active, P, e_out, v_out, info, Vstore,
                                                        warm, tol);
