@@ -15,7 +15,7 @@ __device__ long long g_cnt;
 __device__ long long tick_acc[8];
 __device__ long long tick_last;
 #include "eigh_warp.cuh"
-namespace seqm { std::string g_last_error; unsigned long long g_launches; }
+namespace seqm { int g_check_degeneracy = 0, g_eigh_warp_ring = 0; }
 
 using namespace seqm;
 template <int N>
