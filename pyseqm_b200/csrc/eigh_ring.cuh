@@ -13,13 +13,14 @@
 //   * 2K column slots on K "processors" of R lanes each (R = 2 for m > 16): a processor holds the columns P and Q, a
 //     lane H = N / R rows of both (2H doubles).  A rotation needs one dot product (H FMAs + a shuffle across the R
 //     lanes; the two norms are carried along, updated with every rotation and recomputed once per
-//     sweep) and is applied in the scaled "fast Givens" form, one FMA per element.
+//     sweep) and is applied in the scaled "fast Givens" form as two in-place shears, one FMA per element.
 //   * ordering: RECURSIVE RING.  Phase of group size Kg (K, K/2, .., 1): Kg rounds in which P stays and the Q columns
 //     of a group of Kg processors move on by one processor (so every P meets every Q of its group); then the two
 //     halves of the group exchange one column per processor (all P's to the first half, all Q's to the second) and
 //     the phase repeats inside each half.  K + K/2 + .. + 1 = 2K - 1 rounds per sweep, every pair of columns meets
 //     exactly once, and only ONE column per processor moves per round: (H + 3) doubles per lane by shuffle, no
-//     shared memory, no __syncwarp, all register indices static.
+//     shared memory, no __syncwarp, all register indices static.  (RingCols::phases also takes group sizes that are
+//     not powers of two - used by the two-warp kernel of eigh_ring2_kernels.cu for 20, 24, 28 processors.)
 //   * a pair whose cosine is below 1e-13 and whose angle would still be large (|tan| > 1e-3: both the coupling and the
 //     norm difference are rounding noise, an exactly degenerate cluster) is not rotated, and the carried norms are
 //     updated with the formula that is exact for an inexact tangent.
@@ -30,7 +31,6 @@
 // rotation stays orthogonal to FP64 rounding because c is computed in FP64 from that same t.
 // reference: seqm/seqm_functions/diag.py:102-172 (sym_eig_trunc, construct_P), pack.py:7-41
 #pragma once
-#include <type_traits>
 #include "eigh_warp.cuh"
 
 namespace seqm {
