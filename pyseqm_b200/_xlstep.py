@@ -42,6 +42,7 @@ class XLStep:
         # buffers
         self.xij = torch.empty(topo.npairs, 3, **f64)
         self.rij = torch.empty(topo.npairs, **f64)
+        self._side = torch.cuda.Stream(device=dev)      # second branch of the step (density extrapolation)
         self.w = _ops.WTensors(topo)
         self.M = torch.zeros(B * S * S, 4, 4, **f64)          # only the pair pattern is ever written: zero once
         self.EnucAB = torch.empty(topo.npairs, **f64)
@@ -84,13 +85,21 @@ class XLStep:
         st = _ops._stream()
         n3 = self.x.numel()
         dt = float(md.timestep)
+        # fork: the density extrapolation (reads D and the ring Pt of the previous steps, HBM-bound) does not depend on the
+        # new coordinates, so it runs on a side stream next to the Verlet drift, the pair geometry and the pair pass
+        # (FP64-latency-bound); joined before the Fock build.  Inside a captured graph these are two parallel branches.
+        main = torch.cuda.current_stream()
+        side = self._side
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            check(L.seqm_xl_extrapolate(self.D.numel(), md.m, float(md.coeff_D), self.coeff, _p(self.step_dev), 0,
+                                        _p(self.D), _p(self.Pt), _p(self.P), _ops._stream()), 'seqm_xl_extrapolate')
         check(L.seqm_verlet_kick_drift(n3, dt, _p(self.acc), _p(self.v), _p(self.x), st), 'seqm_verlet_kick_drift')
-        check(L.seqm_xl_extrapolate(self.D.numel(), md.m, float(md.coeff_D), self.coeff, _p(self.step_dev), 0, _p(self.D),
-                                    _p(self.Pt), _p(self.P), st), 'seqm_xl_extrapolate')
         check(L.seqm_pair_geometry(topo.ref(), _p(self.x), self.prep.lcf, _p(self.xij), _p(self.rij), st), 'seqm_pair_geometry')
         ng = _ops.N_GAUSS[self.method]
         check(L.seqm_hcore(topo.ref(), _p(self.prep.atompar), _p(self.xij), _p(self.rij), _p(self.U_ss), _p(self.U_pp), ng,
                            self.w.c, _p(self.M), _p(self.EnucAB), _p(self.pv), st), 'seqm_hcore')
+        main.wait_stream(side)
         check(L.seqm_fock(topo.ref(), self.w.c, _p(self.P), _p(self.M), *[_p(t) for t in self.par5], _p(None), _p(self.F),
                           _p(None), _p(self.pv), _p(None), st), 'seqm_fock')
         if self.use_sp2:
