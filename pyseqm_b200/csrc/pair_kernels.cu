@@ -419,7 +419,10 @@ struct SmemG {
   __device__ __forceinline__ double operator()(int k, int l) const { return g[(k * 10 + l) * PGX_NT]; }
 };
 
-__global__ void __launch_bounds__(PGX_NT)
+#ifndef SEQM_PGX_MINB
+#define SEQM_PGX_MINB 1      // 255 registers, two warps per scheduler (three would need <= 168 registers: 2.7 KB of spills)
+#endif
+__global__ void __launch_bounds__(PGX_NT, SEQM_PGX_MINB)
 pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
                     const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
                     const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
@@ -486,25 +489,23 @@ pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const dou
           }
       }
   }
+  // Compiler fence: without it nvcc forwards the 100 stores above to the reads of rotate_xx_adjoint (same thread,
+  // static indices), i.e. keeps the whole upstream in registers after all: the SASS had 100 STS, not one LDS, and
+  // 2.2 KB of spills (0.58 ms for 256 C60; 0.38 ms with the fence and the overlap adjoint below).
+  asm volatile("" ::: "memory");
   {
-    // overlap part: dE/dM block = 2 X_AB (X = P, or D in the XL-BOMD energy), M = overlap * mean beta
+    // overlap part: dE/dM block = 2 X_AB (X = P, or D in the XL-BOMD energy), M = overlap * mean beta; reverse mode
+    // (overlap_xx_adjoint, pair_math.cuh: radial integrals with one tangent, angular factors with three)
     if (rij[p] <= SEQM_OVERLAP_CUTOFF) {
       const double* Xm = Dmm ? Dmm : Pm;
-      D4 x[3], r;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) { x[c] = D4(xij[3 * p + c]); x[c].d[c] = 1.0; }
-      r = D4(rij[p]);
-      r.d[3] = 1.0;
-      D4 di[16];
-      overlap_block(SEQM_CLS_XX, x, r, a, b, di);
+      double F[16];
 #pragma unroll
       for (int mu = 0; mu < 4; ++mu)
 #pragma unroll
-        for (int nu = 0; nu < 4; ++nu) {
-          const double f = Xm[((size_t)4 * si + mu) * n4 + 4 * sj + nu] * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp));
-#pragma unroll
-          for (int c = 0; c < 4; ++c) eov[c] += f * di[mu * 4 + nu].d[c];
-        }
+        for (int nu = 0; nu < 4; ++nu)
+          F[mu * 4 + nu] = Xm[((size_t)4 * si + mu) * n4 + 4 * sj + nu] * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp));
+      const double xo[3] = {xij[3 * p], xij[3 * p + 1], xij[3 * p + 2]};
+      overlap_xx_adjoint(xo, rij[p], a, b, F, eov);
     }
   }
   typedef Dual<1> D1;

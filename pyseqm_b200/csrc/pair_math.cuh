@@ -261,29 +261,83 @@ SEQM_HD void rotate_xh(const S* ri, const S R[3][3], Sink& sink) {
 // ---------------------------------------------------------------------------------------------
 template <class S>
 SEQM_HD void aux_A(const S& x, S* A) {
-  A[0] = exp_(-x) / x;
+  const S ix = recip_(x);      // one division; the recursions multiply (a few ulp from the divided form)
+  A[0] = exp_(-x) * ix;
 #pragma unroll
-  for (int k = 1; k < 5; ++k) A[k] = A[0] + (double)k * A[k - 1] / x;
+  for (int k = 1; k < 5; ++k) A[k] = A[0] + (double)k * A[k - 1] * ix;
 }
 
 template <class S>
 SEQM_HD void aux_B(const S& x, S* B) {
   const double ax = fabs(val(x));
   if (ax > 0.5) {
-    const S ep = exp_(x) / x, em = -(exp_(-x) / x);
+    const S ix = recip_(x);
+    const S ep = exp_(x) * ix, em = -(exp_(-x) * ix);
     B[0] = ep + em;
 #pragma unroll
-    for (int k = 1; k < 5; ++k) B[k] = ((k % 2 == 0) ? ep : -ep) + em + (double)k * B[k - 1] / x;
+    for (int k = 1; k < 5; ++k) B[k] = ((k % 2 == 0) ? ep : -ep) + em + (double)k * B[k - 1] * ix;
   } else if (ax > 1.0e-6) {
     const S x2 = x * x, x3 = x2 * x, x4 = x2 * x2, x5 = x4 * x, x6 = x3 * x3;
-    B[0] = 2.0 + x2 / 3.0 + x4 / 60.0 + x6 / 2520.0;
-    B[1] = -(2.0 / 3.0) * x - x3 / 15.0 - x5 / 420.0;
-    B[2] = 2.0 / 3.0 + x2 / 5.0 + x4 / 84.0 + x6 / 3240.0;
-    B[3] = -(2.0 / 5.0) * x - x3 / 21.0 - x5 / 540.0;
-    B[4] = 2.0 / 5.0 + x2 / 7.0 + x4 / 108.0 + x6 / 3960.0;
+    // (coefficients as reciprocal constants: a division by a constant that is not a power of two stays a division)
+    B[0] = 2.0 + x2 * (1.0 / 3.0) + x4 * (1.0 / 60.0) + x6 * (1.0 / 2520.0);
+    B[1] = -(2.0 / 3.0) * x - x3 * (1.0 / 15.0) - x5 * (1.0 / 420.0);
+    B[2] = 2.0 / 3.0 + x2 * (1.0 / 5.0) + x4 * (1.0 / 84.0) + x6 * (1.0 / 3240.0);
+    B[3] = -(2.0 / 5.0) * x - x3 * (1.0 / 21.0) - x5 * (1.0 / 540.0);
+    B[4] = 2.0 / 5.0 + x2 * (1.0 / 7.0) + x4 * (1.0 / 108.0) + x6 * (1.0 / 3960.0);
   } else {
     B[0] = S(2.0); B[1] = S(0.0); B[2] = S(2.0 / 3.0); B[3] = S(0.0); B[4] = S(2.0 / 5.0);
   }
+}
+
+// direction cosines of the pair axis and the p-p rotation block (diat_overlap.py:24-45)
+template <class S>
+SEQM_HD void overlap_angles(const S* xij, S u[3], S rot[3][3]) {
+  const S xy2 = xij[0] * xij[0] + xij[1] * xij[1];
+  if (sqrt(val(xy2)) >= 1.0e-10) {
+    const S xy = sqrt_(xy2);
+    const S ixy = recip_(xy);
+    const S ca = xij[0] * ixy, sa = xij[1] * ixy, cb = xij[2], sb = xy;
+    u[0] = ca * sb; u[1] = sa * sb; u[2] = cb;
+    rot[0][0] = sq_(ca * cb) + sa * sa;
+    rot[0][1] = ca * cb * sa * cb - sa * ca;
+    rot[0][2] = -(ca * cb * sb);
+    rot[1][1] = sq_(sa * cb) + ca * ca;
+    rot[1][2] = -(sa * cb * sb);
+    rot[2][2] = sb * sb;
+  } else {
+    const double sg = val(xij[2]) < 0.0 ? -1.0 : (val(xij[2]) > 0.0 ? 1.0 : 0.0);
+    u[0] = S(0.0); u[1] = S(0.0); u[2] = S(sg);
+    rot[0][0] = S(sg * sg * sg * sg); rot[0][1] = S(0.0); rot[0][2] = S(0.0);
+    rot[1][1] = S(sg * sg); rot[1][2] = S(0.0); rot[2][2] = S(0.0);
+  }
+  rot[1][0] = rot[0][1]; rot[2][0] = rot[0][2]; rot[2][1] = rot[1][2];
+}
+
+// the five radial overlap integrals of a heavy-heavy pair: s[0] <s|s>, s[1] <p_sigma|s>, s[2] <s|p_sigma>,
+// s[3] <p_sigma|p_sigma>, s[4] <p_pi|p_pi> (diat_overlap.py:96-230)
+template <class S>
+SEQM_HD void overlap_radial_xx(const S& r, const AtomPar& a, const AtomPar& b, S s[5]) {
+  const double SQ3 = 1.7320508075688772;
+  S A[5], B[5];
+  const S r2 = r * r;
+  const S r4 = r2 * r2;
+  const S r5 = r4 * r;
+  aux_A(0.5 * (a.zs + b.zs) * r, A);
+  aux_B(0.5 * (a.zs - b.zs) * r, B);
+  s[0] = (b.zs25 * a.zs25 * (1.0 / 48.0)) * r5 * (A[4] * B[0] + B[4] * A[0] - 2.0 * (A[2] * B[2]));
+  aux_A(0.5 * (a.zp + b.zs) * r, A);
+  aux_B(0.5 * (a.zp - b.zs) * r, B);
+  s[1] = (b.zs25 * a.zp25 * (1.0 / (16.0 * SQ3))) * r5 *
+         (A[3] * (B[0] - B[2]) - A[1] * (B[2] - B[4]) + B[3] * (A[0] - A[2]) - B[1] * (A[2] - A[4]));
+  aux_A(0.5 * (a.zs + b.zp) * r, A);
+  aux_B(0.5 * (a.zs - b.zp) * r, B);
+  s[2] = (b.zp25 * a.zs25 * (1.0 / (16.0 * SQ3))) * r5 *
+         (A[3] * (B[0] - B[2]) - A[1] * (B[2] - B[4]) - B[3] * (A[0] - A[2]) + B[1] * (A[2] - A[4]));
+  aux_A(0.5 * (a.zp + b.zp) * r, A);
+  aux_B(0.5 * (a.zp - b.zp) * r, B);
+  const S pre = (b.zp25 * a.zp25 / 16.0) * r5;
+  s[3] = -(pre * (B[2] * (A[4] + A[0]) - A[2] * (B[4] + B[0])));
+  s[4] = 0.5 * pre * (A[4] * (B[0] - B[2]) - B[4] * (A[0] - A[2]) - A[2] * B[0] + B[2] * A[0]);
 }
 
 // di[mu*4+nu] = <mu on i | nu on j>.  kind: 0 HH, 1 XH (i heavy, j hydrogen), 2 XX.
@@ -300,29 +354,11 @@ SEQM_HD void overlap_block(int kind, const S* xij, const S& r, const AtomPar& a,
     di[0] = (a.zs15 * b.zs15 * 0.25) * (r2 * r) * (A[2] * B[0] - B[2] * A[0]);
     return;
   }
-  // direction cosines (diat_overlap.py:24-45)
-  const S xy2 = xij[0] * xij[0] + xij[1] * xij[1];
   S u[3], rot[3][3];
-  if (sqrt(val(xy2)) >= 1.0e-10) {
-    const S xy = sqrt_(xy2);
-    const S ca = xij[0] / xy, sa = xij[1] / xy, cb = xij[2], sb = xy;
-    u[0] = ca * sb; u[1] = sa * sb; u[2] = cb;
-    rot[0][0] = sq_(ca * cb) + sa * sa;
-    rot[0][1] = ca * cb * sa * cb - sa * ca;
-    rot[0][2] = -(ca * cb * sb);
-    rot[1][1] = sq_(sa * cb) + ca * ca;
-    rot[1][2] = -(sa * cb * sb);
-    rot[2][2] = sb * sb;
-  } else {
-    const double sg = val(xij[2]) < 0.0 ? -1.0 : (val(xij[2]) > 0.0 ? 1.0 : 0.0);
-    u[0] = S(0.0); u[1] = S(0.0); u[2] = S(sg);
-    rot[0][0] = S(sg * sg * sg * sg); rot[0][1] = S(0.0); rot[0][2] = S(0.0);
-    rot[1][1] = S(sg * sg); rot[1][2] = S(0.0); rot[2][2] = S(0.0);
-  }
-  rot[1][0] = rot[0][1]; rot[2][0] = rot[0][2]; rot[2][1] = rot[1][2];
+  overlap_angles(xij, u, rot);
   const S r4 = r2 * r2;
   if (kind == 1) {
-    di[0] = (b.zs15 * a.zs25 / (SQ3 * 8.0)) * r4 * (A[3] * B[0] - B[3] * A[0] + A[2] * B[1] - B[2] * A[1]);
+    di[0] = (b.zs15 * a.zs25 * (1.0 / (SQ3 * 8.0))) * r4 * (A[3] * B[0] - B[3] * A[0] + A[2] * B[1] - B[2] * A[1]);
     aux_A(0.5 * (a.zp + b.zs) * r, A);
     aux_B(0.5 * (a.zp - b.zs) * r, B);
     const S s211 = (b.zs15 * a.zp25 / 8.0) * r4 * (A[2] * B[0] - B[2] * A[0] + A[3] * B[1] - B[3] * A[1]);
@@ -330,21 +366,10 @@ SEQM_HD void overlap_block(int kind, const S* xij, const S& r, const AtomPar& a,
     for (int m = 0; m < 3; ++m) di[(1 + m) * 4] = s211 * u[m];
     return;
   }
-  const S r5 = r4 * r;
-  di[0] = (b.zs25 * a.zs25 / 48.0) * r5 * (A[4] * B[0] + B[4] * A[0] - 2.0 * (A[2] * B[2]));
-  aux_A(0.5 * (a.zp + b.zs) * r, A);
-  aux_B(0.5 * (a.zp - b.zs) * r, B);
-  const S s211 = (b.zs25 * a.zp25 / (16.0 * SQ3)) * r5 *
-                 (A[3] * (B[0] - B[2]) - A[1] * (B[2] - B[4]) + B[3] * (A[0] - A[2]) - B[1] * (A[2] - A[4]));
-  aux_A(0.5 * (a.zs + b.zp) * r, A);
-  aux_B(0.5 * (a.zs - b.zp) * r, B);
-  const S s121 = (b.zp25 * a.zs25 / (16.0 * SQ3)) * r5 *
-                 (A[3] * (B[0] - B[2]) - A[1] * (B[2] - B[4]) - B[3] * (A[0] - A[2]) + B[1] * (A[2] - A[4]));
-  aux_A(0.5 * (a.zp + b.zp) * r, A);
-  aux_B(0.5 * (a.zp - b.zp) * r, B);
-  const S pre = (b.zp25 * a.zp25 / 16.0) * r5;
-  const S s221 = -(pre * (B[2] * (A[4] + A[0]) - A[2] * (B[4] + B[0])));
-  const S s222 = 0.5 * pre * (A[4] * (B[0] - B[2]) - B[4] * (A[0] - A[2]) - A[2] * B[0] + B[2] * A[0]);
+  S sr[5];
+  overlap_radial_xx(r, a, b, sr);
+  di[0] = sr[0];
+  const S &s211 = sr[1], &s121 = sr[2], &s221 = sr[3], &s222 = sr[4];
 #pragma unroll
   for (int m = 0; m < 3; ++m) {
     di[(1 + m) * 4] = s211 * u[m];
@@ -352,6 +377,37 @@ SEQM_HD void overlap_block(int kind, const S* xij, const S& r, const AtomPar& a,
 #pragma unroll
     for (int n = 0; n < 3; ++n) di[(1 + m) * 4 + 1 + n] = s222 * rot[m][n] - s221 * (u[m] * u[n]);
   }
+}
+
+// Reverse mode of the heavy-heavy overlap block: for E = sum F[mu*4+nu] di[mu*4+nu], out[0..2] = dE/dxij, out[3] = dE/dr.
+// The block separates into radial integrals times angular factors,
+//   E = F00 s0 + s1 c1 - s2 c2 + s4 c3 - s3 c4,   c1 = sum F[p_m][s] u_m,  c2 = sum F[s][p_m] u_m,
+//                                                  c3 = sum F[p_m][p_n] rot_mn,  c4 = sum F[p_m][p_n] u_m u_n,
+// so the radial part (four pairs of auxiliary integrals: the expensive half) carries ONE tangent (d/dr) and the cheap
+// angular part three, instead of four tangents through both and 16 dual-number results.
+SEQM_HD void overlap_xx_adjoint(const double* xij, double r, const AtomPar& a, const AtomPar& b, const double* F,
+                                double* out) {
+  Dual<3> x3[3], u[3], rot[3][3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { x3[c] = Dual<3>(xij[c]); x3[c].d[c] = 1.0; }
+  overlap_angles(x3, u, rot);
+  Dual<3> c1(0.0), c2(0.0), c3(0.0), c4(0.0);
+#pragma unroll
+  for (int m = 0; m < 3; ++m) {
+    c1 = c1 + F[(1 + m) * 4] * u[m];
+    c2 = c2 + F[1 + m] * u[m];
+#pragma unroll
+    for (int n = 0; n < 3; ++n) {
+      c3 = c3 + F[(1 + m) * 4 + 1 + n] * rot[m][n];
+      c4 = c4 + F[(1 + m) * 4 + 1 + n] * (u[m] * u[n]);
+    }
+  }
+  Dual<1> r1(r), s[5];
+  r1.d[0] = 1.0;
+  overlap_radial_xx(r1, a, b, s);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) out[c] = s[1].v * c1.d[c] - s[2].v * c2.d[c] + s[4].v * c3.d[c] - s[3].v * c4.d[c];
+  out[3] = F[0] * s[0].d[0] + s[1].d[0] * c1.v - s[2].d[0] * c2.v + s[4].d[0] * c3.v - s[3].d[0] * c4.v;
 }
 
 // core-core repulsion of one pair (energy.py:38-78); gam = (ss|ss); ngauss = 0 (MNDO), 4 (AM1), 2 (PM3)

@@ -104,4 +104,9 @@ void hc_rotate_xx_adjoint(const double* x, double rv, const double* apar, const 
   auto g = [G](int k, int l) { return G[k * 10 + l]; };
   rotate_xx_adjoint(ri, dri, x, g, out, out[3]);
 }
+
+// reverse-mode adjoint of the heavy-heavy overlap block (overlap_xx_adjoint): out[4] for E = sum F.di
+void hc_overlap_xx_adjoint(const double* x, double rv, const double* apar, const double* bpar, const double* F, double* out) {
+  overlap_xx_adjoint(x, rv, *(const AtomPar*)apar, *(const AtomPar*)bpar, F, out);
+}
 }

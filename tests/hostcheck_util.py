@@ -63,3 +63,11 @@ def rotate_xx_adjoint(x, r, apar, bpar, G):
     G = np.ascontiguousarray(G, dtype=np.float64)
     lib().hc_rotate_xx_adjoint(_p(x), ctypes.c_double(r), _p(apar), _p(bpar), _p(G), _p(out))
     return out
+
+
+def overlap_xx_adjoint(x, r, apar, bpar, F):
+    out = np.zeros(4)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    F = np.ascontiguousarray(F, dtype=np.float64)
+    lib().hc_overlap_xx_adjoint(_p(x), ctypes.c_double(r), _p(apar), _p(bpar), _p(F), _p(out))
+    return out

@@ -114,3 +114,28 @@ def test_rotate_xx_adjoint_matches_forward_duals(aligned):
         assert np.abs(got - ref).max() < 1e-12 * max(1.0, np.abs(ref).max()), (p, got, ref)
         checked += 1
     assert checked >= 6
+
+
+@pytest.mark.parametrize('method', ['MNDO', 'PM3'])
+@pytest.mark.parametrize('aligned', [False, True])
+def test_overlap_xx_adjoint_matches_forward_duals(method, aligned):
+    """overlap_xx_adjoint (radial integrals with one tangent, angular factors with three: what pair_grad_xx_kernel
+    runs) against the four-tangent dual derivative of overlap_block, heavy-heavy pairs, random upstream; short and long
+    distances (both branches of the auxiliary B integrals)"""
+    ni, nj, xij, rij, tab = _pairs_case(method, 13, aligned)
+    Zflat = torch.stack((ni, nj), dim=1).reshape(-1)
+    apars, par, _ = _atompars(tab, method, Zflat.tolist())
+    rng = np.random.RandomState(9)
+    checked = 0
+    for p in range(ni.shape[0]):
+        if int(ni[p]) <= 1 or int(nj[p]) <= 1:
+            continue
+        a, b = apars[2 * p], apars[2 * p + 1]
+        for r in (float(rij[p]), 0.9, 2.3, 12.0):
+            F = rng.standard_normal((4, 4))
+            _, dd, _ = hc.pair_dual(int(ni[p]), int(nj[p]), xij[p].numpy(), r, a, b, 0)
+            ref = np.einsum('mn,mnq->q', F, dd[..., 1:])
+            got = hc.overlap_xx_adjoint(xij[p].numpy(), r, a, b, F)
+            assert np.abs(got - ref).max() < 1e-12 * max(1.0, np.abs(ref).max()), (p, r, got, ref)
+            checked += 1
+    assert checked >= 24
