@@ -26,6 +26,10 @@ import time
 
 
 
+# SEQM_BENCH_CPU=0 skips the CPU-baseline legs (kernel experiments on the GPU box; the driver's runs keep them)
+CPU_LEG = os.environ.get('SEQM_BENCH_CPU', '1') != '0'
+
+
 def host_cores():
     """host threads this process may really use: the scheduler affinity, capped by the cgroup CPU quota (a container
     that sees 24 CPUs but is limited to fewer runs a 24-thread OpenMP region 40x slower than one sized to its quota)"""
@@ -505,7 +509,7 @@ def run_gpu(ctx):
                      "algorithmic_flops_note": "(9 m^3 + 2 m^2 nocc) per eigensolve x (SCF iterations + 1) x molecules"})
     # ---- CPU baseline (rank 0, N = 1 only): the reference's CPU path (oracle/_ref, else the oracle port) on this batch ----
     cpu_base = None
-    if world == 1:
+    if world == 1 and CPU_LEG:
         log("benzene: cpu baseline")
         cpu = CpuPath()
         ns, reps = NMOL, 2
@@ -649,7 +653,7 @@ def run_c60xl(ctx):
                             "frac_of_hbm": nbytes / (ms_ * 1e-3) / 1e9 / hbm}
     ms_step = total_ms / args.steps
     cpu_base, xl_s = None, None
-    if world == 1:      # CPU baselines are an N = 1 item
+    if world == 1 and CPU_LEG:      # CPU baselines are an N = 1 item
         log("xlbomd: cpu baseline")
         cpu = CpuPath()
         spc, xyzc = synth.c60(2, seed=0)
@@ -891,7 +895,7 @@ def run_organics(ctx):
                     "the profiled kernel times of one sweep; the SCF kernels are latency / FP64-issue bound (DESIGN.md), "
                     "one-launch warp SCF %.1f ms of %.1f ms" % (small_ms, tot_prof)}
     cpu_base = None
-    if world == 1:      # CPU baselines are an N = 1 item
+    if world == 1 and CPU_LEG:      # CPU baselines are an N = 1 item
         log("organics: cpu baseline")
         cpu = CpuPath()
         ns = 512

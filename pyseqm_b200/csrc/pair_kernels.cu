@@ -139,12 +139,13 @@ struct StoreSink {
 #ifndef SEQM_PAIRFWD_MINB
 #define SEQM_PAIRFWD_MINB 3      // resident CTAs per SM to compile for (168 registers; measured 17 % faster than 1, tools/build_variant.sh)
 #endif
+constexpr int PAIRFWD_NT = 128;
+// one pair (slot = its position inside the class)
 template <int CLS>
-__global__ void __launch_bounds__(128, SEQM_PAIRFWD_MINB)
-pair_fwd_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
-                const double* __restrict__ rij, int ngauss, double* __restrict__ wc, double* __restrict__ M,
-                double* __restrict__ Enuc, double* __restrict__ pairvec) {
-  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void pair_fwd_pair(int slot, const seqm_topology_t& t, const AtomPar* __restrict__ ap,
+                                              const double* __restrict__ xij, const double* __restrict__ rij, int ngauss,
+                                              double* __restrict__ wc, double* __restrict__ M,
+                                              double* __restrict__ Enuc, double* __restrict__ pairvec) {
   if (slot >= t.ncls[CLS]) return;
   const int p = t.cls_pairs[CLS][slot];
   const int i = t.idxi[p], j = t.idxj[p];
@@ -193,6 +194,32 @@ pair_fwd_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double*
     for (int nu = 0; nu < 4; ++nu)
       Mb[mu * 4 + nu] = di[mu * 4 + nu] * 0.5 * ((mu == 0 ? a.bs : a.bp) + (nu == 0 ? b.bs : b.bp));
   if (Enuc) Enuc[p] = core_repulsion(t.Z[i], t.Z[j], r, gam, a, b, ngauss);
+}
+
+template <int CLS>
+__global__ void __launch_bounds__(PAIRFWD_NT, SEQM_PAIRFWD_MINB)
+pair_fwd_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                const double* __restrict__ rij, int ngauss, double* __restrict__ wc, double* __restrict__ M,
+                double* __restrict__ Enuc, double* __restrict__ pairvec) {
+  pair_fwd_pair<CLS>(blockIdx.x * PAIRFWD_NT + threadIdx.x, t, ap, xij, rij, ngauss, wc, M, Enuc, pairvec);
+}
+
+// All three classes in ONE launch (CTAs [0, nbXX) heavy-heavy, the next nbXH heavy-hydrogen, the rest hydrogen-
+// hydrogen) for batches whose classes each fill less than a wave: there a launch lasts as long as one thread of it, and
+// three launches in a row add those three latencies up (config 2: 33 + 16 + 10 us).  Larger batches keep the separate
+// launches, where the short XH / HH bodies run at their own register count and occupancy.
+__global__ void __launch_bounds__(PAIRFWD_NT, SEQM_PAIRFWD_MINB)
+pair_fwd_all_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                    const double* __restrict__ rij, int ngauss, seqm_w_t w, double* __restrict__ M,
+                    double* __restrict__ Enuc, double* __restrict__ pairvec, int nbXX, int nbXH) {
+  const int b = blockIdx.x;
+  if (b < nbXX)
+    pair_fwd_pair<SEQM_CLS_XX>(b * PAIRFWD_NT + threadIdx.x, t, ap, xij, rij, ngauss, w.wXX, M, Enuc, pairvec);
+  else if (b < nbXX + nbXH)
+    pair_fwd_pair<SEQM_CLS_XH>((b - nbXX) * PAIRFWD_NT + threadIdx.x, t, ap, xij, rij, ngauss, w.wXH, M, Enuc, pairvec);
+  else
+    pair_fwd_pair<SEQM_CLS_HH>((b - nbXX - nbXH) * PAIRFWD_NT + threadIdx.x, t, ap, xij, rij, ngauss, w.wHH, M, Enuc,
+                               pairvec);
 }
 
 // diagonal blocks: U_ss/U_pp + sum over partners of the electron-core attraction, one warp per atom,
@@ -291,12 +318,11 @@ __device__ __forceinline__ void load_diag_packed(const double* __restrict__ X, s
 #define SEQM_PAIRGRAD_MINB 1
 #endif
 template <int CLS>
-__global__ void __launch_bounds__(128, SEQM_PAIRGRAD_MINB)
-pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
-                 const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
-                 const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
-                 double* __restrict__ gx, double* __restrict__ gr) {
-  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void pair_grad_pair(int slot, const seqm_topology_t& t, const AtomPar* __restrict__ ap,
+                                               const double* __restrict__ xij, const double* __restrict__ rij, int ngauss,
+                                               const double* __restrict__ P, const double* __restrict__ Dm,
+                                               const double* __restrict__ gE, const double* __restrict__ gNuc,
+                                               double* __restrict__ gx, double* __restrict__ gr) {
   if (slot >= t.ncls[CLS]) return;
   const int p = t.cls_pairs[CLS][slot];
   const int i = t.idxi[p], j = t.idxj[p];
@@ -399,8 +425,19 @@ pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double
   gr[p] = ge * eel.d[3] + gn * en.d[3];
 }
 
+template <int CLS>
+__global__ void __launch_bounds__(128, SEQM_PAIRGRAD_MINB)
+pair_grad_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                 const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                 const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
+                 double* __restrict__ gx, double* __restrict__ gr) {
+  pair_grad_pair<CLS>(blockIdx.x * blockDim.x + threadIdx.x, t, ap, xij, rij, ngauss, P, Dm, gE, gNuc, gx, gr);
+}
 
 
+
+// the classes of a pair pass share one launch while all their CTAs together stay within this many waves of resident CTAs
+constexpr int PAIR_MERGE_WAVES = 4;
 static int g_pair_grad_reverse = 1;      // 0: forward-mode kernel for heavy-heavy pairs too (test / comparison hook)
 
 // ---------------------------------------------------------------------------------------------
@@ -422,13 +459,13 @@ struct SmemG {
 #ifndef SEQM_PGX_MINB
 #define SEQM_PGX_MINB 1      // 255 registers, two warps per scheduler (three would need <= 168 registers: 2.7 KB of spills)
 #endif
-__global__ void __launch_bounds__(PGX_NT, SEQM_PGX_MINB)
-pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
-                    const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
-                    const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
-                    double* __restrict__ gx, double* __restrict__ gr) {
-  __shared__ double Gs[100 * PGX_NT];
-  const int slot = blockIdx.x * PGX_NT + threadIdx.x;
+// one heavy-heavy pair; Gs: the CTA's [100][PGX_NT] upstream buffer in shared memory
+__device__ __forceinline__ void pair_grad_xx_pair(int slot, double* Gs, const seqm_topology_t& t,
+                                                  const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                                                  const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                                                  const double* __restrict__ Dm, const double* __restrict__ gE,
+                                                  const double* __restrict__ gNuc, double* __restrict__ gx,
+                                                  double* __restrict__ gr) {
   if (slot >= t.ncls[SEQM_CLS_XX]) return;
   const int p = t.cls_pairs[SEQM_CLS_XX][slot];
   const int i = t.idxi[p], j = t.idxj[p];
@@ -530,6 +567,32 @@ pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const dou
   gx[3 * p + 1] = ge * (grot[1] + eov[1]);
   gx[3 * p + 2] = ge * (grot[2] + eov[2]);
   gr[p] = ge * (grr + eov[3]) + gn * en.d[0];
+}
+
+__global__ void __launch_bounds__(PGX_NT, SEQM_PGX_MINB)
+pair_grad_xx_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                    const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                    const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
+                    double* __restrict__ gx, double* __restrict__ gr) {
+  __shared__ double Gs[100 * PGX_NT];
+  pair_grad_xx_pair(blockIdx.x * PGX_NT + threadIdx.x, Gs, t, ap, xij, rij, ngauss, P, Dm, gE, gNuc, gx, gr);
+}
+
+// All three classes in one launch of one-warp CTAs (see pair_fwd_all_kernel): [0, nbXX) heavy-heavy in reverse mode, then
+// heavy-hydrogen and hydrogen-hydrogen with forward duals.
+__global__ void __launch_bounds__(PGX_NT, SEQM_PGX_MINB)
+pair_grad_all_kernel(seqm_topology_t t, const AtomPar* __restrict__ ap, const double* __restrict__ xij,
+                     const double* __restrict__ rij, int ngauss, const double* __restrict__ P,
+                     const double* __restrict__ Dm, const double* __restrict__ gE, const double* __restrict__ gNuc,
+                     double* __restrict__ gx, double* __restrict__ gr, int nbXX, int nbXH) {
+  __shared__ double Gs[100 * PGX_NT];
+  const int b = blockIdx.x;
+  if (b < nbXX)
+    pair_grad_xx_pair(b * PGX_NT + threadIdx.x, Gs, t, ap, xij, rij, ngauss, P, Dm, gE, gNuc, gx, gr);
+  else if (b < nbXX + nbXH)
+    pair_grad_pair<SEQM_CLS_XH>((b - nbXX) * PGX_NT + threadIdx.x, t, ap, xij, rij, ngauss, P, Dm, gE, gNuc, gx, gr);
+  else
+    pair_grad_pair<SEQM_CLS_HH>((b - nbXX - nbXH) * PGX_NT + threadIdx.x, t, ap, xij, rij, ngauss, P, Dm, gE, gNuc, gx, gr);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -660,20 +723,28 @@ int seqm_hcore(const seqm_topology_t* topo, const void* atompar, const double* x
   cudaStream_t st = (cudaStream_t)stream;
   const AtomPar* ap = (const AtomPar*)atompar;
   prof_mark("pair_fwd", st);
-  if (t.ncls[SEQM_CLS_XX] > 0) {
-    SEQM_REQUIRE(w.wXX, "seqm_hcore: wXX null");
-    pair_fwd_kernel<SEQM_CLS_XX><<<cdiv(t.ncls[2], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wXX, M, EnucAB, pairvec);
-    SEQM_CHECK_LAUNCH("pair_fwd_kernel<XX>");
-  }
-  if (t.ncls[SEQM_CLS_XH] > 0) {
-    SEQM_REQUIRE(w.wXH, "seqm_hcore: wXH null");
-    pair_fwd_kernel<SEQM_CLS_XH><<<cdiv(t.ncls[1], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wXH, M, EnucAB, pairvec);
-    SEQM_CHECK_LAUNCH("pair_fwd_kernel<XH>");
-  }
-  if (t.ncls[SEQM_CLS_HH] > 0) {
-    SEQM_REQUIRE(w.wHH, "seqm_hcore: wHH null");
-    pair_fwd_kernel<SEQM_CLS_HH><<<cdiv(t.ncls[0], 128), 128, 0, st>>>(t, ap, xij, rij, ngauss, w.wHH, M, EnucAB, pairvec);
-    SEQM_CHECK_LAUNCH("pair_fwd_kernel<HH>");
+  SEQM_REQUIRE(t.ncls[SEQM_CLS_XX] == 0 || w.wXX, "seqm_hcore: wXX null");
+  SEQM_REQUIRE(t.ncls[SEQM_CLS_XH] == 0 || w.wXH, "seqm_hcore: wXH null");
+  SEQM_REQUIRE(t.ncls[SEQM_CLS_HH] == 0 || w.wHH, "seqm_hcore: wHH null");
+  const long long nbXX = cdiv(t.ncls[2], PAIRFWD_NT), nbXH = cdiv(t.ncls[1], PAIRFWD_NT), nbHH = cdiv(t.ncls[0], PAIRFWD_NT);
+  const int nclasses = (nbXX > 0) + (nbXH > 0) + (nbHH > 0);
+  if (nclasses > 1 && nbXX + nbXH + nbHH <= PAIR_MERGE_WAVES * 148 * SEQM_PAIRFWD_MINB) {
+    pair_fwd_all_kernel<<<(unsigned)(nbXX + nbXH + nbHH), PAIRFWD_NT, 0, st>>>(t, ap, xij, rij, ngauss, w, M, EnucAB, pairvec,
+                                                                             (int)nbXX, (int)nbXH);
+    SEQM_CHECK_LAUNCH("pair_fwd_all_kernel");
+  } else {
+    if (nbXX > 0) {
+      pair_fwd_kernel<SEQM_CLS_XX><<<(unsigned)nbXX, PAIRFWD_NT, 0, st>>>(t, ap, xij, rij, ngauss, w.wXX, M, EnucAB, pairvec);
+      SEQM_CHECK_LAUNCH("pair_fwd_kernel<XX>");
+    }
+    if (nbXH > 0) {
+      pair_fwd_kernel<SEQM_CLS_XH><<<(unsigned)nbXH, PAIRFWD_NT, 0, st>>>(t, ap, xij, rij, ngauss, w.wXH, M, EnucAB, pairvec);
+      SEQM_CHECK_LAUNCH("pair_fwd_kernel<XH>");
+    }
+    if (nbHH > 0) {
+      pair_fwd_kernel<SEQM_CLS_HH><<<(unsigned)nbHH, PAIRFWD_NT, 0, st>>>(t, ap, xij, rij, ngauss, w.wHH, M, EnucAB, pairvec);
+      SEQM_CHECK_LAUNCH("pair_fwd_kernel<HH>");
+    }
   }
   prof_mark("hcore_diag", st);
   if (t.natoms > 0) {
@@ -700,6 +771,15 @@ int seqm_pair_grad(const seqm_topology_t* topo, const void* atompar, const doubl
   cudaStream_t st = (cudaStream_t)stream;
   const AtomPar* ap = (const AtomPar*)atompar;
   prof_mark("pair_grad", st);
+  const long long mXX = cdiv(t.ncls[2], PGX_NT), mXH = cdiv(t.ncls[1], PGX_NT), mHH = cdiv(t.ncls[0], PGX_NT);
+  const int nclasses = (mXX > 0) + (mXH > 0) + (mHH > 0);
+  if (g_pair_grad_reverse && nclasses > 1 && mXX + mXH + mHH <= PAIR_MERGE_WAVES * 148 * 8) {      // 8 one-warp CTAs per SM
+    pair_grad_all_kernel<<<(unsigned)(mXX + mXH + mHH), PGX_NT, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij,
+                                                                       grad_rij, (int)mXX, (int)mXH);
+    SEQM_CHECK_LAUNCH("pair_grad_all_kernel");
+    prof_mark("end", st);
+    return SEQM_OK;
+  }
   if (t.ncls[2] > 0 && g_pair_grad_reverse) {
     pair_grad_xx_kernel<<<cdiv(t.ncls[2], PGX_NT), PGX_NT, 0, st>>>(t, ap, xij, rij, ngauss, P, D, gE, gNuc, grad_xij, grad_rij);
     SEQM_CHECK_LAUNCH("pair_grad_xx_kernel");

@@ -164,10 +164,10 @@ def test_ring_jacobi_against_two_sided_jacobi(name):
     # (methane, ammonia in mixed12) are where they differ most
     assert float((res[1][0] - res[0][0]).abs().cpu()[keep].max()) < 2e-9
     assert float((res[1][1] - res[0][1]).abs().max()) < 1e-10
-    # (N2, whose Pulay coefficients are rounding noise, is left out of the end-to-end comparison like everywhere else:
-    # two runs that differ in the last bit of an integral end 1e-6 eV/A apart on it)
-    assert float((res[1][2] - res[0][2]).abs().cpu()[keep].max()) < 1e-7
-    assert float((res[1][3] - res[0][3]).abs().cpu()[keep].max()) < 1e-6
+    assert float((res[1][2] - res[0][2]).abs().max()) < 1e-7
+    # forces: half the parity bar.  The two-sided solver leaves methane (a triply degenerate occupied level) 1.0e-6 eV/A
+    # from the reference's force, the ring solver 1e-11 (tests/dev/cross_solver_debug.py prints the table)
+    assert float((res[1][3] - res[0][3]).abs().max()) < 5e-6
 
 
 @pytest.mark.parametrize('name', golden_names())
