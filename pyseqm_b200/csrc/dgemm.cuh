@@ -17,6 +17,17 @@ int launch_fock(const seqm_topology_t& t, seqm_w_t w, const double* P, const dou
 // chunked per-molecule reductions for large molecules (fock_kernels.cu): RED_CHUNK elements per CTA, partial sums in
 // scratch [items][chunks], summed in a fixed order
 constexpr int RED_CHUNK = 8192;
+
+// (row, column) of element idx of a matrix with ld columns.  A padded matrix of this library has fewer than 2^32
+// elements (molsize < 16384: checked where molsize enters the library), so the division is written as a 32-bit one; on
+// the size_t index nvcc emits a run-time test for that case around a call into the 64-bit division routine, unrolled
+// with the loop (24 call sites in mix_kernel).
+__device__ __forceinline__ void row_col(size_t idx, int ld, int& i, int& j) {
+  const unsigned u = (unsigned)idx, l = (unsigned)ld;
+  const unsigned q = u / l;
+  i = (int)q;
+  j = (int)(u - q * l);
+}
 int red_chunks(size_t nn);
 int launch_chunk_sum(int items, int chunks, const uint8_t* active, int items_per_mol, const double* part, double* out,
                      const int32_t* out_index, cudaStream_t st);

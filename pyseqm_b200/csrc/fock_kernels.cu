@@ -215,7 +215,8 @@ elec_energy_part_kernel(int S, int chunks, const double* __restrict__ P, const d
   const size_t hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   double acc = 0.0;
   for (size_t idx0 = lo + threadIdx.x; idx0 < hi; idx0 += blockDim.x) {
-    const int ip = (int)(idx0 / n4), j = (int)(idx0 - (size_t)ip * n4);
+    int ip, j;
+    row_col(idx0, n4, ip, j);
     const int i = ip < nh4 ? ip : nh4 + 4 * (ip - nh4);
     const size_t idx = (size_t)i * n4 + j;
     const int ai = i >> 2, mu = i & 3, aj = j >> 2, nu = j & 3;
@@ -358,7 +359,7 @@ int seqm_fock(const seqm_topology_t* topo, seqm_w_t w, const double* P, const do
 
 int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
                      const double* D, int xl, const uint8_t* active, double* E, void* work, void* stream) {
-  SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0, "seqm_elec_energy: bad argument");
+  SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0 && molsize < 16384, "seqm_elec_energy: bad argument");
   SEQM_REQUIRE(!xl || D, "seqm_elec_energy: xl needs D");
   if (nmol == 0) return SEQM_OK;
   return launch_elec_energy(nmol, molsize, P, F, M, D, xl, active, E, (double*)work, (cudaStream_t)stream);
@@ -366,7 +367,7 @@ int seqm_elec_energy(int64_t nmol, int64_t molsize, const double* P, const doubl
 
 int seqm_elec_energy_noalloc(int64_t nmol, int64_t molsize, const double* P, const double* F, const double* M,
                              const double* D, int xl, const uint8_t* active, double* E, void* stream) {
-  SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0, "seqm_elec_energy_noalloc: bad argument");
+  SEQM_REQUIRE(P && F && M && E && nmol >= 0 && molsize > 0 && molsize < 16384, "seqm_elec_energy_noalloc: bad argument");
   SEQM_REQUIRE(!xl || D, "seqm_elec_energy_noalloc: xl needs D");
   if (nmol == 0) return SEQM_OK;
   const size_t nn = (size_t)16 * molsize * molsize;

@@ -66,8 +66,9 @@ mix_kernel(int n4, int chunks, int mode, double alpha, const uint8_t* __restrict
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   const double fac = mode == MIX_ADAPTIVE ? facs[mol] : 0.0;
   for (size_t idx0 = lo + threadIdx.x; idx0 < hi; idx0 += blockDim.x) {
-    const int ip = (int)(idx0 / n4);
-    const size_t idx = (size_t)(ip < nh4 ? ip : nh4 + 4 * (ip - nh4)) * n4 + (idx0 - (size_t)ip * n4);
+    int ip, jp;
+    row_col(idx0, n4, ip, jp);
+    const size_t idx = (size_t)(ip < nh4 ? ip : nh4 + 4 * (ip - nh4)) * n4 + jp;
     const double pn = Pnew[base + idx];
     const double pc = P[base + idx];
     if (mode == MIX_DIRECT) { Pold[base + idx] = pc; P[base + idx] = pn; }
@@ -109,7 +110,8 @@ pack_pair_kernel(int n4, int mld, int chunks, const uint8_t* __restrict__ active
   const size_t tot = (size_t)mld * mld, src = (size_t)mol * n4 * n4, dst = (size_t)mol * tot;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < tot ? lo + RED_CHUNK : tot;
   for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-    const int i = (int)(idx / mld), j = (int)(idx - (size_t)i * mld);
+    int i, j;
+    row_col(idx, mld, i, j);
     double f = 0.0, q = 0.0;
     if (i < m && j < m) {
       const int pi = i < nh4 ? i : nh4 + 4 * (i - nh4), pj = j < nh4 ? j : nh4 + 4 * (j - nh4);
@@ -132,7 +134,8 @@ pulay_store_kernel(int n4, int chunks, int slot, const uint8_t* __restrict__ act
   const size_t dst = ((size_t)mol * NFOCK + slot) * nn;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < nn ? lo + RED_CHUNK : nn;
   for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-    const int i = (int)(idx / n4), j = (int)(idx - (size_t)i * n4);
+    int i, j;
+    row_col(idx, n4, i, j);
     FOCK[dst + idx] = F[src + idx];
     FPPF[dst + idx] = (j >= i) ? G[src + idx] - G[src + (size_t)j * n4 + i] : 0.0;
   }
@@ -249,7 +252,8 @@ pulay_store_packed_kernel(int mld, int chunks, int slot, const uint8_t* __restri
   const size_t src = (size_t)mol * pk, dst = ((size_t)mol * NFOCK + slot) * pk;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < pk ? lo + RED_CHUNK : pk;
   for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-    const int i = (int)(idx / mld), j = (int)(idx - (size_t)i * mld);
+    int i, j;
+    row_col(idx, mld, i, j);
     FOCK[dst + idx] = Fp[src + idx];
     FPPF[dst + idx] = (j >= i) ? Gp[src + idx] - Gp[src + (size_t)j * mld + i] : 0.0;
   }
@@ -272,7 +276,8 @@ pulay_extrapolate_packed_kernel(int n4, int mld, int chunks, int cF, const uint8
   double* out = F + (size_t)mol * n4 * n4;
   const size_t lo = (size_t)chunk * RED_CHUNK, hi = lo + RED_CHUNK < pk ? lo + RED_CHUNK : pk;
   for (size_t idx = lo + threadIdx.x; idx < hi; idx += blockDim.x) {
-    const int i = (int)(idx / mld), j = (int)(idx - (size_t)i * mld);
+    int i, j;
+    row_col(idx, mld, i, j);
     if (i >= m || j >= m) continue;
     double acc = 0.0;
 #pragma unroll
@@ -361,6 +366,7 @@ int seqm_scf(const seqm_topology_t* topo, seqm_w_t w, const double* M, const dou
   SEQM_REQUIRE(opt->converger >= 0 && opt->converger <= 2, "seqm_scf: scf_converger must be [0, alpha], [1] or [2]");
   const seqm_topology_t& t = *topo;
   cudaStream_t st = (cudaStream_t)stream;
+  SEQM_REQUIRE(t.molsize > 0 && t.molsize < 16384, "seqm_scf: molsize out of range (a padded matrix must have fewer than 2^32 elements)");
   const int B = (int)t.nmol, S = (int)t.molsize, n4 = 4 * S;
   const size_t nn = (size_t)n4 * n4;
   if (B == 0) { if (iterations_out) *iterations_out = 0; return SEQM_OK; }

@@ -161,7 +161,8 @@ sp2_x0_kernel(int S, int ld, int rchunks, int chunks, const double* __restrict__
   const size_t e0 = (size_t)chunk * RED_CHUNK, e1 = e0 + RED_CHUNK < tot ? e0 + RED_CHUNK : tot;
   double tr = 0.0, fr = 0.0;
   for (size_t idx = e0 + threadIdx.x; idx < e1; idx += blockDim.x) {
-    const int i = (int)(idx / ld), j = (int)(idx - (size_t)i * ld);
+    int i, j;
+    row_col(idx, ld, i, j);
     double x = 0.0;
     if (i < m && j < m) {
       const double a = Fm[(size_t)pk2pad(i, nh4) * n4 + pk2pad(j, nh4)];
@@ -691,7 +692,7 @@ static int sp2_run(SeqmComm* cm, int nranks, int64_t nmol, int64_t molsize, int 
                    const int32_t* nheavy, const int32_t* nhydro, const int32_t* nocc, double eps,
                    const uint8_t* active, double* D, int32_t* niter, void* work, void* stream,
                    int async_steps = 0, int32_t* d_unfinished = nullptr) {
-  SEQM_REQUIRE(F && nheavy && nhydro && nocc && D && work && nmol >= 0 && molsize > 0, "seqm_sp2_density: bad argument");
+  SEQM_REQUIRE(F && nheavy && nhydro && nocc && D && work && nmol >= 0 && molsize > 0 && molsize < 16384, "seqm_sp2_density: bad argument");
   if (nmol == 0) return SEQM_OK;
   SEQM_REQUIRE(mmax >= 1 && mmax <= 4 * molsize, "seqm_sp2_density: mmax");
   const bool sharded = nranks >= 1;
