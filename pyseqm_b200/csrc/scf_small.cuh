@@ -28,14 +28,13 @@ struct SmallScfArgs {
 };
 
 // exchange block and Coulomb vectors of one pair (fock.py:76-139); P and F packed in shared memory
+// (p = pair index of class slot `slot`, si / sj = the slots of its atoms inside the molecule: three levels of dependent
+// index loads that the caller issues for all class passes at once)
 template <int CLS, int LD>
-__device__ __forceinline__ void small_fock_pair(const SmallScfArgs& A, int mol, int slot, int nh, int nh4,
-                                                const double* __restrict__ Ps, double* __restrict__ Fs) {
+__device__ __forceinline__ void small_fock_pair(const SmallScfArgs& A, int mol, int slot, int p, int si, int sj, int nh,
+                                                int nh4, const double* __restrict__ Ps, double* __restrict__ Fs) {
   const seqm_topology_t& t = A.t;
-  const int p = t.cls_pairs[CLS][slot];
-  const int i = t.idxi[p], j = t.idxj[p];
   const int S = (int)t.molsize;
-  const int si = t.atom_slot[i], sj = t.atom_slot[j];
   const int oi = si < nh ? 4 * si : nh4 + si - nh, oj = sj < nh ? 4 * sj : nh4 + sj - nh;
   const double* Mb = A.M + (((size_t)mol * S + si) * S + sj) * 16;
   double* pv = A.pairvec + (size_t)p * 20;

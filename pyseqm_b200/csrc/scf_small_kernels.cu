@@ -18,6 +18,8 @@ __device__ long long g_phase_last;
     }                                                                              \
   } while (0)
 #endif
+#include <type_traits>
+
 #include "scf_small.cuh"
 #include "eigh_ring.cuh"
 #include "dgemm.cuh"
@@ -33,7 +35,10 @@ __global__ void mol_atom0_kernel(int natoms, int nmol, const int32_t* __restrict
 }
 
 template <int N, bool RING>
-__global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ SmallScfArgs A) {
+// Registers: up to N = 20 the shared buffers leave room for 12 and more CTAs per SM, so those sizes are compiled for 12
+// (168 registers); from N = 24 on shared memory allows 7 - 10 and ptxas may take all 255 (config 2, N = 30: 0.98 ms
+// against 1.03 - 1.06 ms at 168; N = 24 at 168 registers spills 556 bytes).
+__global__ void __launch_bounds__(32, (N <= 20 ? 12 : 8)) scf_small_kernel(const __grid_constant__ SmallScfArgs A) {
   constexpr int LD = WarpLd<N>::value;
   __shared__ __align__(16) double Ps[N * LD];
   __shared__ __align__(16) double S0[N * LD];
@@ -114,6 +119,37 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
   // F(Ps) -> S0, core Hamiltonian -> S1; returns 0.5 sum P (H + F)
   auto fock = [&]() -> double {
     SEQM_PHASE(11);
+    // Descriptors of this lane's first pair in every class pass (XX, XH, XH + 32, HH): class list -> pair -> atoms ->
+    // slots is a chain of three dependent L2 round trips.  Read at the head of each pass it was paid four times per
+    // Fock build by a warp with nothing else to run; here the four chains go out together, level by level, and are in
+    // flight under the core-Hamiltonian copy below.
+    int dp[4], dsi[4], dsj[4];
+    {
+      int di[4], dj[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int c = q == 0 ? SEQM_CLS_XX : (q == 3 ? SEQM_CLS_HH : SEQM_CLS_XH), s = lane + (q == 2 ? 32 : 0);
+        dp[q] = s < cls_n[c] ? t.cls_pairs[c][cls_lo[c] + s] : -1;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        di[q] = dp[q] >= 0 ? t.idxi[dp[q]] : 0;
+        dj[q] = dp[q] >= 0 ? t.idxj[dp[q]] : 0;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        dsi[q] = dp[q] >= 0 ? t.atom_slot[di[q]] : 0;
+        dsj[q] = dp[q] >= 0 ? t.atom_slot[dj[q]] : 0;
+      }
+    }
+    // the same for the diagonal-block pass: atomic number, slot and the two pair ranges of this lane's atom
+    int aZ = 0, aslot = 0, ai0 = 0, ai1 = 0, aj0 = 0, aj1 = 0;
+    if (lane < nat) {
+      const int a = atom0 + lane;
+      aZ = t.Z[a]; aslot = t.atom_slot[a];
+      ai0 = t.start_i[a]; ai1 = t.start_i[a + 1];
+      aj0 = t.start_j[a]; aj1 = t.start_j[a + 1];
+    }
     {      // all N loads of the lane in flight at once (a lone warp has nothing else to hide their latency with)
       double hv[N];
 #pragma unroll
@@ -128,22 +164,43 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
     }
     __syncwarp();
     SEQM_PHASE(1);
-    for (int s = lane; s < cls_n[2]; s += 32) small_fock_pair<SEQM_CLS_XX, LD>(A, mol, cls_lo[2] + s, nh, nh4, Ps, S0);
-    for (int s = lane; s < cls_n[1]; s += 32) small_fock_pair<SEQM_CLS_XH, LD>(A, mol, cls_lo[1] + s, nh, nh4, Ps, S0);
-    for (int s = lane; s < cls_n[0]; s += 32) small_fock_pair<SEQM_CLS_HH, LD>(A, mol, cls_lo[0] + s, nh, nh4, Ps, S0);
+    // iteration `it` of a class pass takes the prefetched descriptor a (it = 0) or b (it = 1 < nq), later ones are read here
+    auto pass = [&](auto cls_tag, int nq, int pa, int sia, int sja, int pb, int sib, int sjb) {
+      constexpr int CLS = decltype(cls_tag)::value;
+#pragma unroll 1
+      for (int s = lane, it = 0; s < cls_n[CLS]; s += 32, ++it) {
+        int p, si, sj;
+        if (it < nq) {
+          p = it == 0 ? pa : pb;
+          si = it == 0 ? sia : sib;
+          sj = it == 0 ? sja : sjb;
+        } else {
+          p = t.cls_pairs[CLS][cls_lo[CLS] + s];
+          si = t.atom_slot[t.idxi[p]];
+          sj = t.atom_slot[t.idxj[p]];
+        }
+        small_fock_pair<CLS, LD>(A, mol, cls_lo[CLS] + s, p, si, sj, nh, nh4, Ps, S0);
+      }
+    };
+    pass(std::integral_constant<int, SEQM_CLS_XX>{}, 1, dp[0], dsi[0], dsj[0], 0, 0, 0);
+    pass(std::integral_constant<int, SEQM_CLS_XH>{}, 2, dp[1], dsi[1], dsj[1], dp[2], dsi[2], dsj[2]);
+    pass(std::integral_constant<int, SEQM_CLS_HH>{}, 1, dp[3], dsi[3], dsj[3], 0, 0, 0);
     __syncwarp();
     SEQM_PHASE(2);
     // diagonal blocks: one-centre terms + the Coulomb vectors of the atom's pairs in pair order
     for (int q = lane; q < nat; q += 32) {
       const int a = atom0 + q;
-      const bool heavy = t.Z[a] > 1;
-      const int s = t.atom_slot[a];
+      const bool pre = q == lane;      // (always, for the <= 32 atoms of a molecule this kernel takes)
+      const bool heavy = (pre ? aZ : t.Z[a]) > 1;
+      const int s = pre ? aslot : t.atom_slot[a];
+      const int ri0 = pre ? ai0 : t.start_i[a], ri1 = pre ? ai1 : t.start_i[a + 1];
+      const int rj0 = pre ? aj0 : t.start_j[a], rj1 = pre ? aj1 : t.start_j[a + 1];
       const int o = s < nh ? 4 * s : nh4 + s - nh;
       double acc[10];
 #pragma unroll
       for (int k = 0; k < 10; ++k) acc[k] = 0.0;
 #pragma unroll 4
-      for (int r = t.start_i[a]; r < t.start_i[a + 1]; ++r) {
+      for (int r = ri0; r < ri1; ++r) {
         const double* pv = A.pairvec + (size_t)r * 20;
         acc[0] += pv[0];
         if (heavy) {
@@ -152,7 +209,7 @@ __global__ void __launch_bounds__(32) scf_small_kernel(const __grid_constant__ S
         }
       }
 #pragma unroll 4
-      for (int r = t.start_j[a]; r < t.start_j[a + 1]; ++r) {
+      for (int r = rj0; r < rj1; ++r) {
         const double* pv = A.pairvec + (size_t)t.perm_j[r] * 20 + 10;
         acc[0] += pv[0];
         if (heavy) {
